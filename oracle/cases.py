@@ -1,0 +1,130 @@
+"""Parity cases shared by the golden generator, the oracle validation and the tests.
+
+TEST INFRASTRUCTURE ONLY.  Each case is: reference constructor arguments, an action list
+(one row per control window, replayed the way the reference driver loop latches them —
+README.md:101-106), an injected-draw tape recipe and a horizon.
+
+Action rows are (servo, target_voltage, current_mode, ON_time, OFF_time)
+(wire_edm.py:84-98,162-170).
+"""
+from __future__ import annotations
+
+import numpy as np
+
+README_CFG = dict(workpiece_height=15.0, wire_diameter=0.25, wire_material="brass",
+                  target_cutting_distance=800.0)          # README.md:45-50
+QUICKSTART_ACTION = [0.1, 80.0, 5, 3.0, 80.0]              # examples/quickstart.py:25-33
+
+
+def make_tape(key: int, n_us: int, forced_ignitions=()) -> np.ndarray:
+    """draws[n_us,5]: u1..u4 uniform [0,1), z5 standard normal (SURVEY §8d cfg 2 recipe).
+
+    forced_ignitions: µs indices whose u3 is set to 0.0 (ignites whenever the env is idle and
+    not shorted on that µs: `u3 < lambda` always holds, ignition.py:327)."""
+    g = np.random.Generator(np.random.Philox(key=key))
+    d = np.empty((n_us, 5), dtype=np.float64)
+    d[:, :4] = g.random((n_us, 4))
+    d[:, 4] = g.standard_normal(n_us)
+    for t in forced_ignitions:
+        d[t, 2] = 0.0
+    return d
+
+
+def never_ignite_tape(n_us: int, ignite_at=(), z=0.0) -> np.ndarray:
+    """Deterministic known-answer tape: u3 = 1.0 (never ignites) except at `ignite_at`."""
+    d = np.empty((n_us, 5), dtype=np.float64)
+    d[:, 0] = 0.5
+    d[:, 1] = 0.5
+    d[:, 2] = 1.0
+    d[:, 3] = 0.5
+    d[:, 4] = z
+    for t in ignite_at:
+        d[t, 2] = 0.0
+    return d
+
+
+def random_actions(key: int, n: int) -> list:
+    """Random actions restricted to odd current modes (even modes raise, material.py:108-113);
+    some values are exactly 0.0 to exercise the falsy defaults (ignition.py:329-343)."""
+    g = np.random.default_rng(key)
+    rows = []
+    for _ in range(n):
+        servo = float(np.float32(g.uniform(-1, 1)))
+        tv = float(np.float32(g.uniform(0, 200))) if g.random() > 0.2 else 0.0
+        mode = int(g.choice([1, 3, 5, 7, 9, 11, 13, 15, 17]))
+        on = float(np.float32(g.uniform(0, 5))) if g.random() > 0.2 else 0.0
+        off = float(np.float32(g.uniform(0, 100))) if g.random() > 0.2 else 0.0
+        rows.append([servo, tv, mode, on, off])
+    return rows
+
+
+# name -> dict(config, mode, params per module, actions, tape=(kind, args), n_us, initial)
+CASES = {
+    # BASELINE cfg 2: README config, quickstart constant action, 20 control steps
+    "cfg2_default": dict(config=README_CFG, mode="position", actions=[QUICKSTART_ACTION],
+                         tape=("philox", 1234), n_us=20000),
+    # BASELINE cfg 1 flavour: actions change every control step, falsy zeros, odd modes
+    "random_actions": dict(config=README_CFG, mode="position", actions=("random", 7, 12),
+                           tape=("philox", 99), n_us=12000),
+    # cfg 3 flavour: position mode, stabilising P gap controller recorded from the reference
+    "gap_controller": dict(config=README_CFG, mode="position", actions=("gap_controller", 25.0),
+                           tape=("philox", 5), n_us=15000),
+    # velocity mode with saturating servo commands (accel/jerk/speed clips, mechanics.py:87-108)
+    "velocity_saturate": dict(config=README_CFG, mode="velocity",
+                              actions=[[100.0, 80.0, 5, 3.0, 80.0], [-4.0e4, 80.0, 5, 3.0, 80.0],
+                                       [3.5e4, 60.0, 3, 2.5, 40.0], [0.0, 80.0, 5, 3.0, 80.0]],
+                              tape=("philox", 11), n_us=6000),
+    # aggressive generator: I17, long ON, short OFF, small gap -> heating, wire break
+    "hot_break": dict(config=dict(README_CFG, initial_gap=12.0), mode="position",
+                      actions=[[0.0, 100.0, 17, 5.0, 6.0]], tape=("philox", 3), n_us=30000),
+    # small initial gap, wire driven into the workpiece: hard shorts (gap<2) and collision
+    "collision": dict(config=dict(README_CFG, initial_gap=6.0), mode="velocity",
+                      actions=[[2.0e4, 80.0, 5, 3.0, 80.0]], tape=("philox", 21), n_us=40000),
+    # debris-choked gap: sigmoid debris shorts + random shorts (ignition.py:115-146,221-242)
+    "debris_shorts": dict(config=dict(README_CFG, initial_gap=8.0), mode="position",
+                          ignition=dict(random_short_max_probability=0.002, base_critical_density=0.01,
+                                        gap_coefficient=0.0005, sigmoid_steepness=300.0),
+                          dielectric=dict(debris_removal_efficiency=0.0002),
+                          actions=[[0.0, 80.0, 9, 3.0, 20.0]], tape=("philox", 8), n_us=15000),
+    # dataclass-default geometry (20 mm / 0.2 mm wire, N=400) with zone mean enabled
+    "dataclass_default_zone_mean": dict(config=dict(), mode="position",
+                                        wire=dict(compute_zone_mean=True, zone_mean_interval=100),
+                                        actions=[[0.05, 90.0, 7, 2.0, 50.0]], tape=("philox", 4), n_us=8000),
+    # BASELINE cfg 5 flavour: 50 mm workpiece, 0.1 mm segments (N=1100), I13, OFF 30
+    "thick_fine": dict(config=dict(workpiece_height=50.0, wire_diameter=0.25, target_cutting_distance=800.0),
+                       mode="position", wire=dict(segment_len=0.1),
+                       actions=[[0.0, 80.0, 13, 3.0, 30.0]], tape=("philox", 15), n_us=6000),
+    # deterministic KAT (i): single forced spark, no unwinding (single_spark_animation.py:214-249)
+    "kat_single_spark": dict(config=README_CFG, mode="position", actions=[[0.0, 80.0, 5, 3.0, 80.0]],
+                             tape=("never", (50,)), n_us=3000, unwind_v=0.0),
+    # deterministic KAT (iii): mechanics step response only, no sparks at all
+    "kat_mechanics_position": dict(config=README_CFG, mode="position", actions=[[1.0, 80.0, 5, 3.0, 80.0], [-1.0, 80.0, 5, 3.0, 80.0]],
+                                   tape=("never", ()), n_us=4000),
+    # target reached: tiny target distance
+    "target_reached": dict(config=dict(README_CFG, initial_gap=10.0, target_cutting_distance=10.004),
+                           mode="position", actions=[[0.0, 80.0, 5, 3.0, 20.0]], tape=("philox", 2), n_us=20000),
+}
+
+
+def case_tape(case: dict) -> np.ndarray:
+    kind, arg = case["tape"]
+    n = case["n_us"]
+    if kind == "philox":
+        return make_tape(arg, n)
+    if kind == "never":
+        return never_ignite_tape(n, ignite_at=arg)
+    raise ValueError(kind)
+
+
+def oracle_overrides(case: dict) -> dict:
+    """Flatten a case into oracle.make_params(**overrides)."""
+    ov = {}
+    for k, v in case.get("config", {}).items():
+        if k == "wire_material":
+            continue
+        ov[k] = v
+    ov["mechanics_control_mode"] = case.get("mode", "position")
+    for grp in ("ignition", "wire", "material", "dielectric", "mechanics"):
+        for k, v in case.get(grp, {}).items():
+            ov[k] = int(v) if isinstance(v, bool) else v
+    return ov
