@@ -1,0 +1,171 @@
+/* sparc_b200.h — C-ABI of the B200-native batched WireEDMEnv step.
+ *
+ * Drop-in boundary for ONE path of geduardo/SPARC: the per-µs physics loop of
+ * `WireEDMEnv.step` (reference src/wedm/envs/wire_edm.py:116-157), i.e. the five
+ * `EDMModule.update(state)` plug-ins (src/wedm/core/module.py:25-29) it calls in fixed order:
+ *   IgnitionModule.update        src/wedm/modules/ignition.py:175-195
+ *   MaterialRemovalModule.update src/wedm/modules/material.py:79-96
+ *   DielectricModule.update      src/wedm/modules/dielectric.py:82-163
+ *   WireModule.update            src/wedm/modules/wire.py:259-347 (+ Numba kernel :58-123)
+ *   MechanicsModule.update       src/wedm/modules/mechanics.py:79-114
+ * plus `_apply_action` (:162-170), the time bookkeeping (:134-144) and `_check_termination`
+ * (:172-179).  The reference has no FFI; the binding a maintainer adds is the ctypes stub in
+ * INTEGRATION.md.  All five modules are fused into one sm_100a kernel that advances every
+ * environment through all µs of a control step.
+ *
+ * Conventions
+ *  - plain C: pointers, sizes, POD structs.  No torch / CUDA types in signatures; a CUDA
+ *    stream is passed as `void*` (cudaStream_t), NULL = default stream.
+ *  - every function returns 0 on success, a negative SPARC_E* code otherwise;
+ *    `sparc_last_error()` gives a thread-local message.  Nothing throws across the boundary.
+ *  - the library owns no device memory: the caller allocates the state blob
+ *    (`sparc_state_bytes`) and passes it to every call.  The library never falls back to the
+ *    CPU; without a CUDA device every compute entry point returns SPARC_E_CUDA.
+ */
+#ifndef SPARC_B200_H
+#define SPARC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPARC_ABI_VERSION 1
+#define SPARC_MAX_MODE 19          /* current modes I1..I19, modules/currents.json */
+#define SPARC_N_DRAW_SLOTS 5       /* u1,u2,u3,u4,z5 per µs — see sparc_step_injected */
+#define SPARC_N_STATS 8
+#define SPARC_N_OBS 8
+
+enum {
+    SPARC_OK = 0,
+    SPARC_E_INVALID = -1,   /* bad argument (NULL pointer, negative size, unsupported geometry) */
+    SPARC_E_CUDA = -2,      /* CUDA runtime error (message in sparc_last_error) */
+    SPARC_E_UNSUPPORTED = -3
+};
+
+/* Per-env flag bits (state field "flags"). */
+enum {
+    SPARC_F_SHORT = 1,          /* EDMState.is_short_circuit */
+    SPARC_F_BROKEN = 2,         /* EDMState.is_wire_broken (thermal break or collision, wire_edm.py:173-175) */
+    SPARC_F_TARGET = 4,         /* EDMState.is_target_distance_reached */
+    SPARC_F_MODE_ERROR = 8,     /* crater table miss: the reference raises ValueError, material.py:108-113 */
+    SPARC_F_HAS_Y = 16,         /* spark_status[1] is not None */
+    SPARC_F_THERMAL_BREAK = 32  /* break came from WireModule._check_wire_breaking (early return, wire_edm.py:129-130) */
+};
+#define SPARC_F_DONE (SPARC_F_BROKEN | SPARC_F_TARGET | SPARC_F_MODE_ERROR)
+
+/* Derived constants of one engine.  Computed on the HOST in Python doubles with the
+ * reference's own expressions (geometry: wire.py:143-252; dielectric.py:57-66;
+ * mechanics.py:48-57; material.py:152-169) so that index quirks such as
+ * `30.0 // 0.2 == 149` are reproduced exactly; the kernel receives numbers, not formulas. */
+typedef struct SparcParams {
+    /* geometry (wire.py:149-156, 208-252) */
+    int32_t n_segments, zone_start, zone_end, actual_zone_start, actual_zone_end;
+    int32_t contact_bottom_idx, contact_top_idx;
+    /* env (env_config.py:18-30) */
+    int32_t servo_interval;
+    int32_t control_mode;             /* 0 position, 1 velocity */
+    /* ignition (ignition.py:17-57) */
+    int32_t debris_short_duration, random_short_duration, default_current_mode;
+    /* dielectric / wire ints */
+    int32_t ion_channel_duration, compute_zone_mean, zone_mean_interval;
+    int32_t reserved0;
+    double initial_gap, target_position, workpiece_height, segment_len;
+    double base_critical_density, gap_coefficient, max_critical_density, hard_short_gap,
+        sigmoid_steepness;
+    double random_short_min_gap, random_short_max_gap, random_short_max_probability;
+    double ignition_a_coeff, ignition_b_coeff, ignition_c_coeff;
+    double default_target_voltage, default_on_time, default_off_time, spark_voltage_factor;
+    /* material: per-mode tables (currents.json, area_corrected.json), index 1..19 */
+    double currents[SPARC_MAX_MODE + 1];
+    double crater_mean[SPARC_MAX_MODE + 1], crater_std[SPARC_MAX_MODE + 1];
+    double kerf_times_height[SPARC_MAX_MODE + 1];   /* (base_overcut + d_wire + depth/1000) * h */
+    int32_t crater_avail[SPARC_MAX_MODE + 1];
+    /* dielectric (dielectric.py:57-66) */
+    double cavity_volume_coeff, reference_gap, debris_obstruction_coeff, debris_removal_per_us,
+        dielectric_temperature;
+    /* wire (wire.py:171-220) */
+    double spool_T, k_cond_coeff, joule_geom_factor, rho_elec, alpha_rho, temp_ref, A, S,
+        temp_update_factor, density_times_cp, plasma_efficiency, base_convection_coefficient,
+        convection_velocity_factor, convection_flow_enhancement;
+    float critical_temperature_f32, breaking_temperature_f32;
+    /* mechanics (mechanics.py:48-57) */
+    double mech_dt, damping_coeff, stiffness_coeff, omega_n, max_acceleration, max_jerk_dt,
+        max_speed;
+} SparcParams;
+
+/* Batched action, SoA device (or host, for *_host entry points) arrays of length n_envs:
+ * the reference's action dict (wire_edm.py:84-98) one array per leaf. */
+typedef struct SparcActions {
+    const float *servo;            /* action["servo"][0] */
+    const float *target_voltage;   /* generator_control.target_voltage[0] */
+    const int32_t *current_mode;   /* generator_control.current_mode[0], 1..19 */
+    const float *on_time;          /* generator_control.ON_time[0] */
+    const float *off_time;         /* generator_control.OFF_time[0] */
+} SparcActions;
+
+/* ---- state blob ------------------------------------------------------------------- */
+/* The state of n_envs environments is ONE caller-owned device allocation, laid out SoA:
+ * one contiguous array per field, temperature field as [n_envs][n_pad] float32.
+ * Field table: name, element type ('d' f64, 'f' f32, 'i' i32), byte offset, element count. */
+int sparc_abi_version(void);
+const char *sparc_last_error(void);
+
+int sparc_num_fields(void);
+/* name/dtype of field `idx`; offset/count for a given (n_envs, n_segments). */
+int sparc_field_info(int idx, int n_envs, int n_segments, const char **name, char *dtype,
+                     size_t *byte_offset, size_t *count);
+size_t sparc_state_bytes(int n_envs, int n_segments);
+int sparc_padded_segments(int n_segments);   /* row pitch (floats) of the temperature field */
+
+/* ---- compute entry points (all asynchronous on `stream`) --------------------------- */
+
+/* First-time initialisation of a freshly allocated blob: every env gets the state of a newly
+ * constructed WireEDMEnv after reset() and episode counter 0. */
+int sparc_init(void *state, const SparcParams *p, int n_envs, void *stream);
+
+/* EDMState() + WireEDMEnv.reset() (wire_edm.py:106-114) + fresh module state for the envs whose
+ * mask byte is non-zero (mask == NULL: all).  `episode` increments for reset envs. */
+int sparc_reset(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream);
+
+/* n_us reference step() calls for every env, on-device Philox4x32-10 draws keyed by
+ * (seed, env_id_base + env, episode, µs).  Envs already terminated are left untouched.
+ * `actions` is latched inside the loop exactly when the reference latches it
+ * (time_since_servo >= servo_interval, wire_edm.py:117-121). */
+int sparc_step(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+               uint64_t seed, uint32_t env_id_base, void *stream);
+
+/* Same, with the random draws injected: draws_dev[env][t][5] doubles, t = 0..n_us-1 for THIS
+ * call; slots: u1 debris-short roll (ignition.py:233), u2 random-short roll (:239), u3 ignition
+ * roll (:327), u4 spark location uniform (:261), z5 crater standard normal (material.py:127). */
+int sparc_step_injected(void *state, const SparcParams *p, const SparcActions *actions, int n_envs,
+                        int n_us, const double *draws_dev, void *stream);
+
+/* Observation summary of the last step call, obs_dev[SPARC_N_OBS][n_envs] float32:
+ * 0 gap [µm], 1 wire_velocity [µm/s], 2 mean voltage over the call [V], 3 sparks ignited in the
+ * call, 4 short-circuit µs in the call, 5 max wire temperature [K], 6 debris_density, 7 flags. */
+int sparc_observe(const void *state, int n_envs, int n_segments, float *obs_dev, void *stream);
+
+/* Sum over envs of [sparks, short µs, short events, crater µm³, short pulses, env-µs simulated,
+ * broken, target reached] -> out_dev[8] doubles (for the NCCL all-reduce of episode stats). */
+int sparc_reduce_stats(const void *state, int n_envs, int n_segments, double *out_dev8, void *stream);
+
+/* Host-buffer convenience (the reference-facing call): H2D of the five action arrays, n_us
+ * steps, D2H of the observation summary, then a stream sync.  Pointers are HOST pointers
+ * (pinned for full speed); `scratch_dev` is caller-owned device scratch of
+ * sparc_host_scratch_bytes(n_envs) bytes. */
+size_t sparc_host_scratch_bytes(int n_envs);
+int sparc_step_host(void *state, const SparcParams *p, const SparcActions *actions_host, int n_envs,
+                    int n_us, uint64_t seed, uint32_t env_id_base, void *scratch_dev,
+                    float *obs_host, void *stream);
+
+/* Kernel launch geometry chosen for (n_envs, n_segments): lanes per env, slots per lane,
+ * threads per block, blocks.  For reporting / tests. */
+int sparc_launch_info(int n_envs, int n_segments, int32_t out[4]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPARC_B200_H */

@@ -1,0 +1,369 @@
+// sparc_b200.cu — C-ABI (include/sparc_b200.h) over the fused sm_100a step kernel.
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared
+//        -Xcompiler -fPIC  (see sparc_b200/build.py).  -fmad=false keeps the fp64 scalar path
+// free of contraction so it rounds like the reference's Python floats; the fp32 stencil uses
+// explicit fmaf().
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "../../include/sparc_b200.h"
+#include "state_layout.h"
+#include "step_kernel.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, const char *detail = "")
+{
+    snprintf(g_err, sizeof(g_err), fmt, detail);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char *what)
+{
+    snprintf(g_err, sizeof(g_err), "%s: %s", what, cudaGetErrorString(e));
+    return SPARC_E_CUDA;
+}
+
+#define CUDA_TRY(expr)                                      \
+    do {                                                    \
+        cudaError_t _e = (expr);                            \
+        if (_e != cudaSuccess) return cuda_fail(_e, #expr); \
+    } while (0)
+
+struct FieldDesc {
+    const char *name;
+    char dtype;
+    size_t elem;
+};
+
+const FieldDesc kFields[] = {
+#define X(name, ctype, dt, init) {#name, dt, sizeof(ctype)},
+    SPARC_STATE_FIELDS(X)
+#undef X
+    {"episode", 'i', sizeof(int32_t)},
+    {"T", 'f', sizeof(float)},
+};
+constexpr int kNumFields = (int)(sizeof(kFields) / sizeof(kFields[0]));
+
+constexpr size_t kAlign = 256;
+
+int padded_segments(int n_segments) { return (int)sparc_align_up((size_t)n_segments, 32); }
+
+// offset of field idx; idx == kNumFields gives total bytes
+size_t field_offset(int idx, int n_envs, int n_segments)
+{
+    size_t off = 0;
+    for (int i = 0; i < idx; i++) {
+        size_t count = (size_t)n_envs;
+        if (i == kNumFields - 1) count = (size_t)n_envs * padded_segments(n_segments);
+        off = sparc_align_up(off + count * kFields[i].elem, kAlign);
+    }
+    return off;
+}
+
+SparcStatePtrs make_ptrs(void *state, int n_envs, int n_segments)
+{
+    SparcStatePtrs S;
+    char *base = (char *)state;
+    int idx = 0;
+#define X(name, ctype, dt, init) S.name = (ctype *)(base + field_offset(idx++, n_envs, n_segments));
+    SPARC_STATE_FIELDS(X)
+#undef X
+    S.episode = (int32_t *)(base + field_offset(idx++, n_envs, n_segments));
+    S.T = (float *)(base + field_offset(idx++, n_envs, n_segments));
+    S.n_pad = padded_segments(n_segments);
+    return S;
+}
+
+// ---- small kernels --------------------------------------------------------------------------
+__global__ void reset_kernel(const __grid_constant__ SparcParams P, SparcStatePtrs S, int n_envs,
+                             const uint8_t *mask, int first_time)
+{
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n_envs) return;
+    if (mask && !mask[e]) return;
+#define X(name, ctype, dt, init) S.name[e] = (ctype)(init);
+    SPARC_STATE_FIELDS(X)
+#undef X
+    S.episode[e] = first_time ? 0 : S.episode[e] + 1;
+}
+
+__global__ void reset_T_kernel(SparcStatePtrs S, int n_envs, float spool, const uint8_t *mask)
+{
+    size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    size_t total = (size_t)n_envs * S.n_pad;
+    if (idx >= total) return;
+    int e = (int)(idx / S.n_pad);
+    if (mask && !mask[e]) return;
+    S.T[idx] = spool;
+}
+
+// one warp per env: max over the temperature row + scalar gather
+__global__ void observe_kernel(SparcStatePtrs S, int n_envs, int n_segments, float *obs)
+{
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (warp >= n_envs) return;
+    const float *row = S.T + (size_t)warp * S.n_pad;
+    float m = -3.0e38f;
+    for (int i = lane; i < n_segments; i += 32) m = fmaxf(m, row[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) {
+        int e = warp;
+        int steps = S.win_steps[e];
+        obs[0 * (size_t)n_envs + e] = (float)(S.wp[e] - S.wire[e]);
+        obs[1 * (size_t)n_envs + e] = (float)S.v[e];
+        obs[2 * (size_t)n_envs + e] = steps > 0 ? (float)(S.win_vsum[e] / (double)steps) : 0.0f;
+        obs[3 * (size_t)n_envs + e] = (float)S.win_sparks[e];
+        obs[4 * (size_t)n_envs + e] = (float)S.win_short_us[e];
+        obs[5 * (size_t)n_envs + e] = m;
+        obs[6 * (size_t)n_envs + e] = (float)S.debris_density[e];
+        obs[7 * (size_t)n_envs + e] = (float)S.flags[e];
+    }
+}
+
+__global__ void reduce_stats_kernel(SparcStatePtrs S, int n_envs, double *out)
+{
+    double acc[SPARC_N_STATS] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < n_envs; e += gridDim.x * blockDim.x) {
+        int fl = S.flags[e];
+        acc[0] += S.stat_sparks[e];
+        acc[1] += S.stat_short_us[e];
+        acc[2] += S.stat_short_events[e];
+        acc[3] += S.stat_crater_sum[e];
+        acc[4] += S.stat_pulse_short[e];
+        acc[5] += S.stat_steps[e];
+        acc[6] += (fl & SPARC_F_BROKEN) ? 1.0 : 0.0;
+        acc[7] += (fl & SPARC_F_TARGET) ? 1.0 : 0.0;
+    }
+#pragma unroll
+    for (int k = 0; k < SPARC_N_STATS; k++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+        if ((threadIdx.x & 31) == 0) atomicAdd(&out[k], acc[k]);
+    }
+}
+
+// ---- step kernel dispatch -------------------------------------------------------------------
+using StepFn = void (*)(const SparcParams, const SparcStatePtrs, const sparc::StepArgs);
+
+struct Variant {
+    int K, L;
+    StepFn fn[2];   // [INJECT]
+};
+
+#define VARIANT(K, L) {K, L, {sparc::step_kernel<K, L, false>, sparc::step_kernel<K, L, true>}}
+const Variant kVariants[] = {
+    VARIANT(4, 32), VARIANT(8, 32), VARIANT(12, 32), VARIANT(13, 32), VARIANT(16, 32),
+    VARIANT(20, 32), VARIANT(24, 32), VARIANT(28, 32), VARIANT(36, 32),
+    VARIANT(24, 16), VARIANT(26, 16),
+};
+constexpr int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
+
+const Variant *pick_variant(int n_segments)
+{
+    int M = n_segments - 1;
+    int want_L = 32;
+    if (const char *s = getenv("SPARC_LANES_PER_ENV")) want_L = atoi(s);
+    const Variant *best = nullptr;
+    for (int i = 0; i < kNumVariants; i++) {
+        const Variant &v = kVariants[i];
+        if (v.L != want_L || v.K * v.L < M) continue;
+        if (!best || v.K < best->K) best = &v;
+    }
+    if (!best && want_L != 32) {
+        for (int i = 0; i < kNumVariants; i++) {
+            const Variant &v = kVariants[i];
+            if (v.L != 32 || v.K * v.L < M) continue;
+            if (!best || v.K < best->K) best = &v;
+        }
+    }
+    return best;
+}
+
+int check_common(const void *state, const SparcParams *p, int n_envs)
+{
+    if (!state || !p) return fail(SPARC_E_INVALID, "null state/params pointer");
+    if (n_envs <= 0) return fail(SPARC_E_INVALID, "n_envs must be positive");
+    if (p->n_segments < 2) return fail(SPARC_E_UNSUPPORTED, "n_segments < 2 is not supported");
+    return SPARC_OK;
+}
+
+int launch_step(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+                uint64_t seed, uint32_t env_id_base, const double *draws, void *stream)
+{
+    int rc = check_common(state, p, n_envs);
+    if (rc) return rc;
+    if (!actions || !actions->servo || !actions->target_voltage || !actions->current_mode ||
+        !actions->on_time || !actions->off_time)
+        return fail(SPARC_E_INVALID, "null action array");
+    if (n_us < 0) return fail(SPARC_E_INVALID, "n_us must be >= 0");
+    if (n_us == 0) return SPARC_OK;
+    const Variant *v = pick_variant(p->n_segments);
+    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large for the register-resident kernel");
+    sparc::StepArgs a;
+    a.act = *actions;
+    a.n_envs = n_envs;
+    a.n_us = n_us;
+    a.seed = seed;
+    a.env_id_base = env_id_base;
+    a.draws = draws;
+    SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
+    int G = 32 / v->L;
+    int warps = (n_envs + G - 1) / G;
+    int wpb = SPARC_BLOCK_THREADS / 32;
+    int blocks = (warps + wpb - 1) / wpb;
+    v->fn[draws ? 1 : 0]<<<blocks, SPARC_BLOCK_THREADS, 0, (cudaStream_t)stream>>>(*p, S, a);
+    CUDA_TRY(cudaGetLastError());
+    return SPARC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sparc_abi_version(void) { return SPARC_ABI_VERSION; }
+const char *sparc_last_error(void) { return g_err; }
+int sparc_num_fields(void) { return kNumFields; }
+int sparc_padded_segments(int n_segments) { return padded_segments(n_segments); }
+
+int sparc_field_info(int idx, int n_envs, int n_segments, const char **name, char *dtype,
+                     size_t *byte_offset, size_t *count)
+{
+    if (idx < 0 || idx >= kNumFields) return fail(SPARC_E_INVALID, "field index out of range");
+    if (n_envs <= 0 || n_segments <= 0) return fail(SPARC_E_INVALID, "bad n_envs/n_segments");
+    if (name) *name = kFields[idx].name;
+    if (dtype) *dtype = kFields[idx].dtype;
+    if (byte_offset) *byte_offset = field_offset(idx, n_envs, n_segments);
+    if (count) *count = (idx == kNumFields - 1) ? (size_t)n_envs * padded_segments(n_segments) : (size_t)n_envs;
+    return SPARC_OK;
+}
+
+size_t sparc_state_bytes(int n_envs, int n_segments)
+{
+    if (n_envs <= 0 || n_segments <= 0) return 0;
+    return field_offset(kNumFields, n_envs, n_segments);
+}
+
+static int do_reset(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream,
+                    int first_time)
+{
+    int rc = check_common(state, p, n_envs);
+    if (rc) return rc;
+    SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
+    cudaStream_t st = (cudaStream_t)stream;
+    reset_kernel<<<(n_envs + 127) / 128, 128, 0, st>>>(*p, S, n_envs, mask_dev, first_time);
+    size_t total = (size_t)n_envs * S.n_pad;
+    reset_T_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(S, n_envs, (float)p->spool_T, mask_dev);
+    CUDA_TRY(cudaGetLastError());
+    return SPARC_OK;
+}
+
+int sparc_init(void *state, const SparcParams *p, int n_envs, void *stream)
+{
+    return do_reset(state, p, n_envs, nullptr, stream, 1);
+}
+
+int sparc_reset(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream)
+{
+    return do_reset(state, p, n_envs, mask_dev, stream, 0);
+}
+
+int sparc_step(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+               uint64_t seed, uint32_t env_id_base, void *stream)
+{
+    return launch_step(state, p, actions, n_envs, n_us, seed, env_id_base, nullptr, stream);
+}
+
+int sparc_step_injected(void *state, const SparcParams *p, const SparcActions *actions, int n_envs,
+                        int n_us, const double *draws_dev, void *stream)
+{
+    if (!draws_dev) return fail(SPARC_E_INVALID, "null draws pointer");
+    return launch_step(state, p, actions, n_envs, n_us, 0, 0, draws_dev, stream);
+}
+
+int sparc_observe(const void *state, int n_envs, int n_segments, float *obs_dev, void *stream)
+{
+    if (!state || !obs_dev || n_envs <= 0 || n_segments <= 0) return fail(SPARC_E_INVALID, "bad observe arguments");
+    SparcStatePtrs S = make_ptrs((void *)state, n_envs, n_segments);
+    int threads = 128;
+    int blocks = (int)(((size_t)n_envs * 32 + threads - 1) / threads);
+    observe_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(S, n_envs, n_segments, obs_dev);
+    CUDA_TRY(cudaGetLastError());
+    return SPARC_OK;
+}
+
+int sparc_reduce_stats(const void *state, int n_envs, int n_segments, double *out_dev8, void *stream)
+{
+    if (!state || !out_dev8 || n_envs <= 0 || n_segments <= 0) return fail(SPARC_E_INVALID, "bad reduce arguments");
+    SparcStatePtrs S = make_ptrs((void *)state, n_envs, n_segments);
+    cudaStream_t st = (cudaStream_t)stream;
+    CUDA_TRY(cudaMemsetAsync(out_dev8, 0, sizeof(double) * SPARC_N_STATS, st));
+    int blocks = (n_envs + 255) / 256;
+    if (blocks > 148 * 4) blocks = 148 * 4;
+    reduce_stats_kernel<<<blocks, 256, 0, st>>>(S, n_envs, out_dev8);
+    CUDA_TRY(cudaGetLastError());
+    return SPARC_OK;
+}
+
+size_t sparc_host_scratch_bytes(int n_envs)
+{
+    if (n_envs <= 0) return 0;
+    size_t n = sparc_align_up((size_t)n_envs * 4, kAlign);
+    return n * 5 + sparc_align_up((size_t)n_envs * 4 * SPARC_N_OBS, kAlign);
+}
+
+int sparc_step_host(void *state, const SparcParams *p, const SparcActions *ah, int n_envs, int n_us,
+                    uint64_t seed, uint32_t env_id_base, void *scratch_dev, float *obs_host, void *stream)
+{
+    int rc = check_common(state, p, n_envs);
+    if (rc) return rc;
+    if (!ah || !scratch_dev || !obs_host) return fail(SPARC_E_INVALID, "null host action / scratch / obs pointer");
+    cudaStream_t st = (cudaStream_t)stream;
+    size_t n = sparc_align_up((size_t)n_envs * 4, kAlign);
+    char *d = (char *)scratch_dev;
+    SparcActions ad;
+    ad.servo = (const float *)(d + 0 * n);
+    ad.target_voltage = (const float *)(d + 1 * n);
+    ad.current_mode = (const int32_t *)(d + 2 * n);
+    ad.on_time = (const float *)(d + 3 * n);
+    ad.off_time = (const float *)(d + 4 * n);
+    float *obs_dev = (float *)(d + 5 * n);
+    size_t bytes = (size_t)n_envs * 4;
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.servo, ah->servo, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.target_voltage, ah->target_voltage, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.current_mode, ah->current_mode, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.on_time, ah->on_time, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.off_time, ah->off_time, bytes, cudaMemcpyHostToDevice, st));
+    rc = launch_step(state, p, &ad, n_envs, n_us, seed, env_id_base, nullptr, stream);
+    if (rc) return rc;
+    rc = sparc_observe(state, n_envs, p->n_segments, obs_dev, stream);
+    if (rc) return rc;
+    CUDA_TRY(cudaMemcpyAsync(obs_host, obs_dev, bytes * SPARC_N_OBS, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return SPARC_OK;
+}
+
+int sparc_launch_info(int n_envs, int n_segments, int32_t out[4])
+{
+    if (!out || n_envs <= 0 || n_segments < 2) return fail(SPARC_E_INVALID, "bad launch_info arguments");
+    const Variant *v = pick_variant(n_segments);
+    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large for the register-resident kernel");
+    int G = 32 / v->L;
+    int warps = (n_envs + G - 1) / G;
+    int wpb = SPARC_BLOCK_THREADS / 32;
+    out[0] = v->L;
+    out[1] = v->K;
+    out[2] = SPARC_BLOCK_THREADS;
+    out[3] = (warps + wpb - 1) / wpb;
+    return SPARC_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,83 @@
+// state_layout.h — SoA layout of the per-env state inside the caller-owned blob.
+//
+// One X-macro drives the field table (sparc_field_info), the pointer struct the kernels
+// receive, and the reset kernel.  Fields mirror the reference's EDMState
+// (src/wedm/core/state.py:25-91) plus the module-internal state that the reference keeps on
+// the module objects (ignition.py:75-83, material.py:46-47, dielectric.py:69-80,
+// wire.py:204-225, mechanics.py:60) — SURVEY.md §8 a5/a6.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+// X(name, ctype, dtype_char, reset_value_expression)   — `P` is the SparcParams in scope.
+#define SPARC_STATE_FIELDS(X)                                                                     \
+    /* positions / mechanics (fp64: per-µs increments are ~1e-5 µm on 1e2 µm) */     \
+    X(wp, double, 'd', P.initial_gap)              /* EDMState.workpiece_position [µm] */          \
+    X(wire, double, 'd', 0.0)                      /* EDMState.wire_position [µm] */               \
+    X(v, double, 'd', 0.0)                         /* EDMState.wire_velocity [µm/s] */             \
+    X(prev_accel, double, 'd', 0.0)                /* MechanicsModule.prev_accel */                \
+    /* electrical */                                                                              \
+    X(voltage, double, 'd', 0.0)                   /* EDMState.voltage (None -> 0) */              \
+    X(current, double, 'd', 0.0)                   /* EDMState.current (None -> 0) */              \
+    /* latched action (0.0 == None == "use default", ignition.py:329-343) */                      \
+    X(target_voltage, double, 'd', 0.0)                                                           \
+    X(on_time, double, 'd', 0.0)                                                                  \
+    X(off_time, double, 'd', 0.0)                                                                 \
+    X(target_delta, double, 'd', 0.0)                                                             \
+    X(unwind_v, double, 'd', 0.2)                  /* EDMState.wire_unwinding_velocity */          \
+    /* dielectric */                                                                              \
+    X(debris_volume, double, 'd', 0.0)                                                            \
+    X(debris_density, double, 'd', 0.0)                                                           \
+    X(cavity_volume, double, 'd', 0.0)                                                            \
+    X(flow, double, 'd', 0.0)                      /* EDMState.flow_rate == module flow_condition */\
+    X(last_crater_volume, double, 'd', 0.0)                                                       \
+    X(spark_y, double, 'd', -1.0)                  /* spark_status[1] [mm] */                      \
+    X(d_last_gap, double, 'd', -1.0)               /* DielectricModule._last_gap_um */             \
+    X(d_last_density, double, 'd', -1.0)           /* DielectricModule._last_debris_density */     \
+    X(w_last_flow, double, 'd', 0.0)               /* WireModule._last_flow_condition */           \
+    X(wire_avg_T, double, 'd', 0.0)                /* EDMState.wire_average_temperature */         \
+    X(w_last_zone_mean, double, 'd', P.spool_T)    /* WireModule._last_zone_mean */                \
+    X(ign_cached_value, double, 'd', 60.0)         /* IgnitionModule._cached_current_value */      \
+    X(stat_crater_sum, double, 'd', 0.0)           /* sum of crater volumes [µm³] */               \
+    X(win_vsum, double, 'd', 0.0)                  /* sum of voltage over the last step call */    \
+    /* convection coefficients: the two distinct values of WireModule.h_eff_zone (float32) */     \
+    X(h_base, float, 'f', 0.0f)                                                                   \
+    X(h_enh, float, 'f', 0.0f)                                                                    \
+    /* integer state */                                                                           \
+    X(time, int32_t, 'i', 0)                                                                      \
+    X(t_servo, int32_t, 'i', 0)                                                                   \
+    X(t_open_v, int32_t, 'i', 0)                                                                  \
+    X(t_spark_ign, int32_t, 'i', 0)                                                               \
+    X(t_spark_end, int32_t, 'i', 0)                                                               \
+    X(spark_state, int32_t, 'i', 0)                /* spark_status[0]: 0 idle, 1 spark, -1 short, -2 rest */ \
+    X(spark_dur, int32_t, 'i', 0)                  /* spark_status[2] */                           \
+    X(rand_short_rem, int32_t, 'i', 0)                                                            \
+    X(deb_short_rem, int32_t, 'i', 0)                                                             \
+    X(ion_rem, int32_t, 'i', 0)                                                                   \
+    X(crit_count, int32_t, 'i', 0)                 /* EDMState.time_in_critical_temp */            \
+    X(current_mode, int32_t, 'i', 0)               /* 0 None, k = "I<k>", -1 = "I0" */             \
+    X(ign_cached_mode, int32_t, 'i', 0)                                                           \
+    X(mat_cached_mode, int32_t, 'i', 0)                                                           \
+    X(mat_info_mode, int32_t, 'i', 1)              /* crater_data["I1"], material.py:47 */         \
+    X(w_zone_counter, int32_t, 'i', 0)                                                            \
+    X(flags, int32_t, 'i', 0)                                                                     \
+    X(stat_sparks, int32_t, 'i', 0)                                                               \
+    X(stat_short_us, int32_t, 'i', 0)                                                             \
+    X(stat_short_events, int32_t, 'i', 0)                                                         \
+    X(stat_pulse_short, int32_t, 'i', 0)                                                          \
+    X(stat_steps, int32_t, 'i', 0)                 /* step() calls executed this episode */        \
+    X(win_sparks, int32_t, 'i', 0)                                                                \
+    X(win_short_us, int32_t, 'i', 0)                                                              \
+    X(win_steps, int32_t, 'i', 0)
+
+// `episode` is the only field that survives a reset (it is incremented instead).
+struct SparcStatePtrs {
+#define X(name, ctype, dt, init) ctype *name;
+    SPARC_STATE_FIELDS(X)
+#undef X
+    int32_t *episode;
+    float *T;       // [n_envs][n_pad]
+    int32_t n_pad;
+};
+
+static inline size_t sparc_align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }

@@ -1,0 +1,160 @@
+"""Batched engine: owns the device state blob (torch memory) and drives the C-ABI.
+
+PyTorch is plumbing here — device allocation, streams, pinned host buffers.  All arithmetic
+happens in the sm_100a kernels behind include/sparc_b200.h.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .params import SparcParams
+
+_TORCH_DTYPE = {"d": torch.float64, "f": torch.float32, "i": torch.int32}
+_ELEM = {"d": 8, "f": 4, "i": 4}
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+class Engine:
+    """State of `n_envs` environments on one CUDA device + the step/observe/reset calls."""
+
+    def __init__(self, n_envs: int, params: SparcParams, device="cuda:0", seed: int = 0,
+                 env_id_base: int = 0):
+        if not torch.cuda.is_available():
+            raise N.SparcError("sparc_b200 needs a CUDA device (there is no CPU fallback)")
+        self.lib = N.lib()
+        self.n_envs = int(n_envs)
+        self.params = params
+        self.n_segments = int(params.n_segments)
+        self.device = torch.device(device)
+        self.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+        self.env_id_base = int(env_id_base)
+        nbytes = self.lib.sparc_state_bytes(self.n_envs, self.n_segments)
+        if nbytes == 0:
+            raise N.SparcError("bad n_envs / n_segments")
+        with torch.cuda.device(self.device):
+            self.blob = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)
+            self.n_pad = self.lib.sparc_padded_segments(self.n_segments)
+            self.fields: Dict[str, torch.Tensor] = {}
+            for name, dt, off, cnt in N.field_table(self.n_envs, self.n_segments):
+                view = self.blob[off: off + cnt * _ELEM[dt]].view(_TORCH_DTYPE[dt])
+                if name == "T":
+                    view = view.view(self.n_envs, self.n_pad)
+                self.fields[name] = view
+            # action staging (device) + pinned host mirrors for the host-buffer path
+            self._act_dev = {
+                "servo": torch.zeros(self.n_envs, dtype=torch.float32, device=self.device),
+                "target_voltage": torch.zeros(self.n_envs, dtype=torch.float32, device=self.device),
+                "current_mode": torch.zeros(self.n_envs, dtype=torch.int32, device=self.device),
+                "on_time": torch.zeros(self.n_envs, dtype=torch.float32, device=self.device),
+                "off_time": torch.zeros(self.n_envs, dtype=torch.float32, device=self.device),
+            }
+            self.obs_dev = torch.zeros(N.N_OBS, self.n_envs, dtype=torch.float32, device=self.device)
+            self.stats_dev = torch.zeros(N.N_STATS, dtype=torch.float64, device=self.device)
+            self._scratch = torch.zeros(self.lib.sparc_host_scratch_bytes(self.n_envs), dtype=torch.uint8,
+                                        device=self.device)
+            self._act_host = {k: torch.zeros(self.n_envs, dtype=v.dtype).pin_memory() for k, v in self._act_dev.items()}
+            self.obs_host = torch.zeros(N.N_OBS, self.n_envs, dtype=torch.float32).pin_memory()
+            N.check(self.lib.sparc_init(self.blob.data_ptr(), C.byref(self.params), self.n_envs, self._stream()))
+
+    # ------------------------------------------------------------------------------------------
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def __getitem__(self, name: str) -> torch.Tensor:
+        return self.fields[name]
+
+    @property
+    def T(self) -> torch.Tensor:
+        """Wire temperature field, [n_envs, n_segments] float32 view of the live state."""
+        return self.fields["T"][:, : self.n_segments]
+
+    def launch_info(self) -> dict:
+        out = (C.c_int32 * 4)()
+        N.check(self.lib.sparc_launch_info(self.n_envs, self.n_segments, out))
+        return dict(lanes_per_env=out[0], cells_per_lane=out[1], block_threads=out[2], blocks=out[3])
+
+    def reset(self, mask: Optional[torch.Tensor] = None) -> None:
+        """Fresh-env state for the masked envs (all when mask is None)."""
+        m = None
+        if mask is not None:
+            m = mask.to(device=self.device, dtype=torch.uint8).contiguous()
+        with torch.cuda.device(self.device):
+            N.check(self.lib.sparc_reset(self.blob.data_ptr(), C.byref(self.params), self.n_envs, _ptr(m), self._stream()))
+
+    def set_actions(self, servo, target_voltage, current_mode, on_time, off_time) -> None:
+        """Copy one batched action (any array-likes broadcastable to [n_envs]) to the device."""
+        for key, val in (("servo", servo), ("target_voltage", target_voltage), ("current_mode", current_mode),
+                         ("on_time", on_time), ("off_time", off_time)):
+            dst = self._act_dev[key]
+            if isinstance(val, torch.Tensor):
+                src = val.reshape(-1) if val.numel() > 1 else val.reshape(())
+                dst.copy_(src.to(dtype=dst.dtype), non_blocking=True)
+            else:
+                arr = np.asarray(val)
+                if arr.size == 1:
+                    dst.fill_(arr.reshape(()).item())
+                else:
+                    dst.copy_(torch.from_numpy(np.ascontiguousarray(arr.reshape(-1))).to(dst.dtype), non_blocking=True)
+
+    def _actions_struct(self, bufs) -> N.SparcActions:
+        return N.SparcActions(bufs["servo"].data_ptr(), bufs["target_voltage"].data_ptr(),
+                              bufs["current_mode"].data_ptr(), bufs["on_time"].data_ptr(),
+                              bufs["off_time"].data_ptr())
+
+    def step(self, n_us: int, draws: Optional[torch.Tensor] = None) -> None:
+        """Advance every env by n_us reference step() calls with the staged device actions.
+
+        draws: optional [n_envs, n_us, 5] float64 device tensor of injected random draws."""
+        a = self._actions_struct(self._act_dev)
+        with torch.cuda.device(self.device):
+            if draws is None:
+                N.check(self.lib.sparc_step(self.blob.data_ptr(), C.byref(self.params), C.byref(a), self.n_envs,
+                                            int(n_us), self.seed, self.env_id_base, self._stream()))
+            else:
+                assert draws.dtype == torch.float64 and draws.is_contiguous() and draws.device == self.blob.device
+                assert tuple(draws.shape) == (self.n_envs, int(n_us), N.N_DRAW_SLOTS)
+                N.check(self.lib.sparc_step_injected(self.blob.data_ptr(), C.byref(self.params), C.byref(a),
+                                                     self.n_envs, int(n_us), draws.data_ptr(), self._stream()))
+
+    def step_host(self, n_us: int) -> torch.Tensor:
+        """Host-buffer path: pinned host actions -> device, n_us steps, observation -> pinned host.
+
+        Fill `engine.host_actions[...]` first.  Synchronises the stream; returns obs_host [8, n_envs]."""
+        a = self._actions_struct(self._act_host)
+        with torch.cuda.device(self.device):
+            N.check(self.lib.sparc_step_host(self.blob.data_ptr(), C.byref(self.params), C.byref(a), self.n_envs,
+                                             int(n_us), self.seed, self.env_id_base, self._scratch.data_ptr(),
+                                             self.obs_host.data_ptr(), self._stream()))
+        return self.obs_host
+
+    @property
+    def host_actions(self) -> Dict[str, torch.Tensor]:
+        return self._act_host
+
+    def observe(self) -> torch.Tensor:
+        """[8, n_envs] float32 device tensor: gap, wire velocity, mean voltage of the last call,
+        sparks and short-circuit µs in the last call, max wire temperature, debris density, flags."""
+        with torch.cuda.device(self.device):
+            N.check(self.lib.sparc_observe(self.blob.data_ptr(), self.n_envs, self.n_segments,
+                                           self.obs_dev.data_ptr(), self._stream()))
+        return self.obs_dev
+
+    def reduce_stats(self) -> torch.Tensor:
+        """fp64[8] device tensor: sparks, short µs, short events, crater µm³, short pulses,
+        env-µs simulated, broken envs, target-reached envs (summed over this engine's envs)."""
+        with torch.cuda.device(self.device):
+            N.check(self.lib.sparc_reduce_stats(self.blob.data_ptr(), self.n_envs, self.n_segments,
+                                                self.stats_dev.data_ptr(), self._stream()))
+        return self.stats_dev
+
+    def bytes_per_control_step(self) -> int:
+        """Algorithmic HBM bytes one step call moves: the whole state read once and written once."""
+        return 2 * int(self.blob.numel())

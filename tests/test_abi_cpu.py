@@ -1,0 +1,101 @@
+"""CPU-side checks: the C-ABI library loads and exports every declared symbol, the state
+layout is sane, host-side constant derivation reproduces the reference geometry quirks."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+from oracle import oracle as O
+
+
+@pytest.fixture(scope="module")
+def native():
+    from sparc_b200 import build, _native
+
+    build.build()
+    return _native
+
+
+def test_library_exports_every_declared_symbol(native):
+    header = open(os.path.join(ROOT, "include", "sparc_b200.h")).read()
+    declared = set(re.findall(r"\b(sparc_[a-z_0-9]+)\s*\(", header))
+    assert declared, "no declarations parsed"
+    L = native.lib()
+    for sym in sorted(declared):
+        assert hasattr(L, sym), f"{sym} declared in include/sparc_b200.h but not exported"
+    assert set(native.EXPORTS) == declared
+    assert L.sparc_abi_version() == 1
+
+
+def test_params_struct_size_matches_c(native):
+    """ctypes mirror and C struct agree (field_info works, state bytes are consistent)."""
+    from sparc_b200.params import SparcParams
+
+    # sizeof(SparcParams) as the compiler sees it is embedded in the layout of kernel params;
+    # check a derived quantity instead: offsets are monotonically increasing and aligned.
+    tab = native.field_table(1000, 375)
+    offs = [t[2] for t in tab]
+    assert offs == sorted(offs) and all(o % 256 == 0 for o in offs)
+    name, dt, off, cnt = tab[-1]
+    assert name == "T" and dt == "f" and cnt == 1000 * native.lib().sparc_padded_segments(375)
+    assert native.lib().sparc_state_bytes(1000, 375) >= off + cnt * 4
+    assert C.sizeof(SparcParams) % 8 == 0
+
+
+def test_bad_arguments_return_error_codes(native):
+    L = native.lib()
+    assert L.sparc_state_bytes(0, 375) == 0
+    assert L.sparc_field_info(999, 1, 375, None, None, None, None) == -1
+    assert b"out of range" in L.sparc_last_error()
+    out = (C.c_int32 * 4)()
+    assert L.sparc_launch_info(4096, 375, out) == 0
+    assert out[0] * out[1] >= 374
+    assert L.sparc_launch_info(4096, 100000, out) == -3
+
+
+@pytest.mark.parametrize("cfg,wire", [
+    (dict(workpiece_height=15.0, wire_diameter=0.25), {}),
+    ({}, {}),
+    (dict(workpiece_height=50.0, wire_diameter=0.25), dict(segment_len=0.2)),
+    (dict(workpiece_height=50.0, wire_diameter=0.25), dict(segment_len=0.1)),
+    (dict(workpiece_height=50.0, wire_diameter=0.25), dict(segment_len=0.05)),
+    (dict(workpiece_height=7.3, wire_diameter=0.1), dict(segment_len=0.13, buffer_len_bottom=12.0, contact_offset_top=40.0)),
+])
+def test_host_geometry_matches_oracle(cfg, wire):
+    from sparc_b200 import params as P
+
+    p = P.derive_params(P.EnvironmentConfig(**cfg), "position", wire=P.WireModuleParameters(**wire))
+    g = O.OracleEnv(**cfg, **wire).geometry()
+    assert (p.n_segments, p.zone_start, p.zone_end, p.contact_bottom_idx, p.contact_top_idx) == \
+        (g["n"], g["zone_start"], g["zone_end"], g["contact_bottom"], g["contact_top"])
+
+
+def test_config_api_matches_reference_contract(tmp_path):
+    from sparc_b200 import params as P
+
+    c = P.EnvironmentConfig(workpiece_height=15.0)
+    c.to_json(tmp_path / "c.json")
+    assert P.EnvironmentConfig.from_json(tmp_path / "c.json") == c
+    assert P.EnvironmentConfig.from_dict({"initial_gap": 7.0, "junk": 1}).initial_gap == 7.0
+    with pytest.raises(ValueError, match="workpiece_height must be positive"):
+        P.EnvironmentConfig(workpiece_height=0).validate()
+    with pytest.raises(ValueError, match="max_wire_temperature"):
+        P.EnvironmentConfig(max_wire_temperature=200).validate()
+    with pytest.raises(ValueError, match="mechanics_control_mode"):
+        P.derive_params(P.EnvironmentConfig(), "torque")
+    with pytest.raises(ValueError, match="Unknown wire material"):
+        P.derive_params(P.EnvironmentConfig(wire_material="unobtainium"))
+
+
+def test_action_window_latch_timing():
+    import parity_util as PU
+
+    acts = ["a0", "a1", "a2"]
+    assert PU.action_for_window(acts, 0, 1000) == "a0"        # first ms never latches
+    assert PU.action_for_window(acts, 1000, 1000) == "a0"     # latch 1 (entry time 1000) uses actions[0]
+    assert PU.action_for_window(acts, 2000, 1000) == "a1"
+    assert PU.action_for_window(acts, 2999, 2) == "a2"
+    assert PU.action_for_window(acts, 9000, 1000) == "a2"

@@ -1,0 +1,106 @@
+"""Parity of the CUDA path (through the C-ABI) against the committed reference trajectories and
+against the C oracle, with the reference's random draws injected (BASELINE cfg 2 protocol).
+
+Discrete events must match exactly; fp64 scalars to 1e-12; the float32 temperature field within
+|dT| <= 2e-3 K + 1e-5*|T| (measured errors are printed and are far smaller).
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_DIR
+from oracle import cases as CS
+import parity_util as PU
+
+pytestmark = pytest.mark.gpu
+
+
+def _golden(name):
+    return np.load(os.path.join(GOLDEN_DIR, f"{name}.npz"))
+
+
+@pytest.mark.parametrize("name", sorted(CS.CASES))
+def test_trajectory_matches_reference_golden(name):
+    """µs-by-µs (1-µs launches) for the first 3000 µs, then at every 50th µs, against the
+    fixtures generated from the unmodified reference."""
+    import torch
+
+    g = _golden(name)
+    case = CS.CASES[name]
+    tape = CS.case_tape(case)
+    actions = g["actions"]
+    eng = PU.make_engine(case, n_envs=3)
+    # env 0 and 2 replay the case; env 1 gets a different tape (must not disturb its neighbours)
+    tapes = np.stack([tape, np.roll(tape, 17, axis=0), tape])
+    draws = torch.from_numpy(tapes).to(eng.device)
+    rows = g["f64_rows"]
+    n_done = int(g["n_done"][0])
+    done = 0
+    max_t_err = 0.0
+    for r in rows:
+        n = int(r) + 1 - done
+        PU.stage_action(eng, PU.action_for_window(actions, done, n))
+        eng.step(n, draws[:, done:done + n].contiguous())
+        done += n
+        f, i = PU.read_rows(eng, envs=(0, 2))
+        k = int(np.searchsorted(rows, r))
+        for env_row in range(2):
+            PU.assert_rows_match(f[env_row], i[env_row], g["f64"][k], g["i32"][r].astype(np.int64),
+                                 where=f"{name} after {done} µs env {env_row * 2}")
+        max_t_err = max(max_t_err, abs(f[0, -1] - g["f64"][k, -1]))
+    assert done == n_done
+    print(f"\n[{name}] {n_done} µs matched; max |tmax_gpu - tmax_ref| = {max_t_err:.3e} K")
+
+
+@pytest.mark.parametrize("name", sorted(CS.CASES))
+def test_control_step_launches_match_oracle(name):
+    """1000-µs launches (the production path) against the oracle: every scalar and the whole
+    temperature field at each control-step boundary."""
+    import torch
+
+    g = _golden(name)
+    case = CS.CASES[name]
+    actions = g["actions"]
+    orc_env, tape, orc = PU.run_oracle_case(case, actions, rec_every=1000, t_every=1000)
+    eng = PU.make_engine(case, n_envs=5)
+    draws = torch.from_numpy(np.stack([tape] * 5)).to(eng.device)
+    n_us = case["n_us"]
+    si = 1000
+    worst = 0.0
+    for w, t0 in enumerate(range(0, n_us, si)):
+        n = min(si, n_us - t0)
+        PU.stage_action(eng, PU.action_for_window(actions, t0, n))
+        eng.step(n, draws[:, t0:t0 + n].contiguous())
+        f, i = PU.read_rows(eng, envs=(0, 4))
+        if w >= len(orc["f64"]):
+            break
+        for env_row in range(2):
+            PU.assert_rows_match(f[env_row], i[env_row], orc["f64"][w], orc["i32"][w].astype(np.int64),
+                                 where=f"{name} window {w} env {env_row * 4}")
+        T_gpu = eng.T[0].cpu().numpy()
+        T_ref = orc["T"][w]
+        err = np.abs(T_gpu.astype(np.float64) - T_ref.astype(np.float64))
+        worst = max(worst, float(err.max()))
+        assert np.all(err <= PU.T_ATOL + PU.T_RTOL * np.abs(T_ref)), f"{name} window {w}: max dT {err.max()}"
+        if i[0, -1]:
+            break
+    print(f"\n[{name}] max |T_gpu - T_oracle| over all snapshots = {worst:.3e} K")
+
+
+def test_even_mode_sets_error_flag():
+    """Crater data exists for odd modes only: the reference raises ValueError at the first spark
+    (material.py:108-113); the kernel freezes the env and raises the mode-error flag."""
+    import torch
+    from sparc_b200 import _native as N
+
+    case = dict(config=CS.README_CFG, mode="position")
+    eng = PU.make_engine(case, n_envs=2)
+    tape = CS.never_ignite_tape(3000, ignite_at=(1500,))
+    draws = torch.from_numpy(np.stack([tape, tape])).to(eng.device)
+    eng.set_actions(0.0, 80.0, np.array([6, 5]), 3.0, 80.0)
+    for t0 in range(0, 3000, 1000):
+        eng.step(1000, draws[:, t0:t0 + 1000].contiguous())
+    flags = eng["flags"].cpu().numpy()
+    assert flags[0] & N.F_MODE_ERROR and not (flags[1] & N.F_MODE_ERROR)
+    assert eng["time"].cpu().numpy().tolist() == [1500, 3000]
