@@ -161,6 +161,11 @@ int sparc_step_host(void *state, const SparcParams *p, const SparcActions *actio
                     int n_us, uint64_t seed, uint32_t env_id_base, void *scratch_dev,
                     float *obs_host, void *stream);
 
+/* Measured FP32 FMA issue peak of the current device [TFLOP/s] (dense FFMA micro-kernel, a few
+ * ms; synchronous).  Roofline denominator for the compute-bound step kernel; scratch_dev needs
+ * >= 4 MiB of device memory. */
+int sparc_measure_fp32_peak(void *scratch_dev, size_t scratch_bytes, double *tflops_out);
+
 /* Kernel launch geometry chosen for (n_envs, n_segments): lanes per env, slots per lane,
  * threads per block, blocks.  For reporting / tests. */
 int sparc_launch_info(int n_envs, int n_segments, int32_t out[4]);

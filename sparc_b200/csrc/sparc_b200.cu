@@ -151,6 +151,22 @@ __global__ void reduce_stats_kernel(SparcStatePtrs S, int n_envs, double *out)
     }
 }
 
+// FP32 issue-rate probe: 8 independent FFMA chains per thread (roofline denominator)
+__global__ void fma_peak_kernel(float *out, float a, float b, int iters)
+{
+    float x[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) x[i] = threadIdx.x * 1e-3f + i;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) x[i] = fmaf(x[i], a, b);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s += x[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 // ---- step kernel dispatch -------------------------------------------------------------------
 using StepFn = void (*)(const SparcParams, const SparcStatePtrs, const sparc::StepArgs);
 
@@ -348,6 +364,35 @@ int sparc_step_host(void *state, const SparcParams *p, const SparcActions *ah, i
     if (rc) return rc;
     CUDA_TRY(cudaMemcpyAsync(obs_host, obs_dev, bytes * SPARC_N_OBS, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
+    return SPARC_OK;
+}
+
+int sparc_measure_fp32_peak(void *scratch_dev, size_t scratch_bytes, double *tflops_out)
+{
+    if (!scratch_dev || !tflops_out) return fail(SPARC_E_INVALID, "null scratch/out pointer");
+    int dev = 0, sms = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const int threads = 512, bpsm = 4, iters = 1 << 16;
+    int blocks = sms * bpsm;
+    if ((size_t)blocks * threads * sizeof(float) > scratch_bytes) return fail(SPARC_E_INVALID, "scratch too small");
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 4; rep++) {
+        CUDA_TRY(cudaEventRecord(e0, 0));
+        fma_peak_kernel<<<blocks, threads>>>((float *)scratch_dev, 1.0001f, 0.5f, iters);
+        CUDA_TRY(cudaEventRecord(e1, 0));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+        double tf = 2.0 * 8.0 * iters * (double)blocks * threads / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *tflops_out = best;
     return SPARC_OK;
 }
 

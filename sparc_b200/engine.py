@@ -158,3 +158,12 @@ class Engine:
     def bytes_per_control_step(self) -> int:
         """Algorithmic HBM bytes one step call moves: the whole state read once and written once."""
         return 2 * int(self.blob.numel())
+
+
+def measure_fp32_peak(device="cuda:0") -> float:
+    """Measured FP32 FMA peak [TFLOP/s] of `device` (roofline denominator for the step kernel)."""
+    out = C.c_double(0.0)
+    with torch.cuda.device(device):
+        scratch = torch.empty(8 << 20, dtype=torch.uint8, device=device)
+        N.check(N.lib().sparc_measure_fp32_peak(scratch.data_ptr(), scratch.numel(), C.byref(out)))
+    return float(out.value)
