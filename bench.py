@@ -193,11 +193,11 @@ def run_gpu_arm(args):
         torch.cuda.synchronize(dev)
 
     # ---- device-resident arm ------------------------------------------------------------------
+    sampler = ClockSampler(local_rank)
+    sampler.start()                                 # samples cover warm-up + timed region (all under load)
     for _ in range(max(args.warmup, 3)):
         eng.step(si)
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
     K = args.steps
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     launches = 0
