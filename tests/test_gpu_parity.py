@@ -104,3 +104,39 @@ def test_even_mode_sets_error_flag():
     flags = eng["flags"].cpu().numpy()
     assert flags[0] & N.F_MODE_ERROR and not (flags[1] & N.F_MODE_ERROR)
     assert eng["time"].cpu().numpy().tolist() == [1500, 3000]
+
+
+@pytest.mark.parametrize("cfg_name,n_us", [("cfg2_default", 30000), ("hot_break", 20000), ("debris_shorts", 12000)])
+def test_on_device_philox_matches_oracle_philox(cfg_name, n_us):
+    """Production path (on-device Philox4x32-10 draws, quiet-µs fast path): the oracle implements
+    the same counter-based stream, so trajectories must agree event-for-event."""
+    from oracle import oracle as O
+
+    case = CS.CASES[cfg_name]
+    action = [float(np.float32(x)) for x in case["actions"][0]]
+    seed, base, n_envs = 0x1234567887654321, 1000, 6
+    from sparc_b200.engine import Engine
+
+    eng = Engine(n_envs, PU.case_params(case), seed=seed, env_id_base=base)
+    PU.stage_action(eng, action)
+    orcs = [O.OracleEnv(**CS.oracle_overrides(case)) for _ in range(n_envs)]
+    alive = [True] * n_envs
+    worst = 0.0
+    for t0 in range(0, n_us, 1000):
+        eng.step(1000)
+        f, i = PU.read_rows(eng, envs=range(n_envs))
+        T = eng.T.cpu().numpy()
+        for e in range(n_envs):
+            if alive[e]:
+                res = orcs[e].run(1000, [action], draws=None, seed=seed, env_id=base + e, rec_every=0)
+                alive[e] = res["n_done"] == 1000
+            fo, io = orcs[e].record(0)
+            io = io.astype(np.int64)
+            io[-1] = int(io[11] or io[12])
+            PU.assert_rows_match(f[e], i[e], fo, io, where=f"{cfg_name} philox env {e} t0 {t0}")
+            err = np.abs(T[e].astype(np.float64) - orcs[e].temperature.astype(np.float64))
+            worst = max(worst, float(err.max()))
+            assert np.all(err <= PU.T_ATOL + PU.T_RTOL * np.abs(orcs[e].temperature))
+    sparks = int(eng["stat_sparks"].sum().item())
+    assert sparks > 0
+    print(f"\n[{cfg_name}] philox mode: {sparks} sparks over {n_envs} envs, max |dT| {worst:.3e} K")
