@@ -7,7 +7,7 @@ import os
 from .params import SparcParams
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "_lib", "libsparc_b200.so")
+LIB_PATH = os.environ.get("SPARC_LIB_PATH") or os.path.join(HERE, "_lib", "libsparc_b200.so")
 
 N_OBS = 8
 N_STATS = 8

@@ -414,7 +414,16 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
 }
 
 // resident blocks per SM the register budget is sized for (65536 regs / (128 thr * blocks))
-constexpr int min_blocks_for(int K) { return K <= 13 ? 4 : (K <= 20 ? 3 : 2); }
+#ifndef SPARC_MINB_SMALL
+#define SPARC_MINB_SMALL 4
+#endif
+#ifndef SPARC_MINB_MID
+#define SPARC_MINB_MID 3
+#endif
+#ifndef SPARC_MINB_BIG
+#define SPARC_MINB_BIG 2
+#endif
+constexpr int min_blocks_for(int K) { return K <= 13 ? SPARC_MINB_SMALL : (K <= 20 ? SPARC_MINB_MID : SPARC_MINB_BIG); }
 
 template <int K, int L, bool INJECT>
 __global__ void __launch_bounds__(SPARC_BLOCK_THREADS, min_blocks_for(K))
