@@ -1,0 +1,4 @@
+from .batched import BatchedWireEDMEnv  # noqa: F401
+from .wire_edm import WireEDMEnv  # noqa: F401
+
+__all__ = ["WireEDMEnv", "BatchedWireEDMEnv"]

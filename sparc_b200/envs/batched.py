@@ -1,0 +1,153 @@
+"""`BatchedWireEDMEnv`: the vectorised N-environment surface (new; the reference has none).
+
+One `step(actions)` = one control step: the fused kernel advances every environment through
+`servo_interval` µs (1000 reference `WireEDMEnv.step()` calls per env) in one launch.  The
+action is latched inside the kernel exactly when the reference latches it
+(time_since_servo >= servo_interval, wire_edm.py:117-121), so with the reference's
+"first millisecond" quirk the very first control step still runs on the generator defaults
+unless `latch_first_action=True` (default) arms the latch at reset.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+
+from .. import _native as N
+from ..engine import Engine
+from ..params import (DielectricModuleParameters, EnvironmentConfig, IgnitionModuleParameters,
+                      MaterialModuleParameters, MechanicsModuleParameters, WireModuleParameters,
+                      derive_params, load_craters)
+
+OBS_KEYS = ("gap", "wire_velocity", "mean_voltage", "sparks", "short_us", "max_temperature", "debris_density")
+
+
+class BatchedWireEDMEnv:
+    """N independent Wire-EDM environments on one GPU.
+
+    actions: dict with the reference's structure (wire_edm.py:84-98); every leaf is an array /
+    tensor of length n_envs (or a scalar, broadcast):
+        {"servo": ..., "generator_control": {"target_voltage": ..., "current_mode": ...,
+                                              "ON_time": ..., "OFF_time": ...}}
+    """
+
+    def __init__(self, n_envs: int, *, device="cuda:0", mechanics_control_mode: str = "position",
+                 config: EnvironmentConfig = None, ignition_params: IgnitionModuleParameters = None,
+                 wire_params: WireModuleParameters = None, material_params: MaterialModuleParameters = None,
+                 dielectric_params: DielectricModuleParameters = None,
+                 mechanics_params: MechanicsModuleParameters = None, seed: int = 0, env_id_base: int = 0,
+                 latch_first_action: bool = True, auto_reset: bool = False):
+        if mechanics_control_mode not in ["position", "velocity"]:
+            raise ValueError(f"mechanics_control_mode must be 'position' or 'velocity', got {mechanics_control_mode}")
+        self.config = config or EnvironmentConfig()
+        self.config.validate()
+        self.mechanics_control_mode = mechanics_control_mode
+        self.n_envs = int(n_envs)
+        self.servo_interval = int(self.config.servo_interval)
+        self.dt = self.config.dt
+        self.latch_first_action = bool(latch_first_action)
+        self.auto_reset = bool(auto_reset)
+        self.params = derive_params(self.config, mechanics_control_mode, ignition_params, wire_params,
+                                    material_params, dielectric_params, mechanics_params)
+        self.engine = Engine(self.n_envs, self.params, device=device, seed=seed, env_id_base=env_id_base)
+        self._valid_modes = sorted(int(k[1:]) for k in load_craters())
+        self._arm_latch(None)
+
+    # ------------------------------------------------------------------------------------------
+    @property
+    def device(self):
+        return self.engine.device
+
+    @property
+    def n_segments(self) -> int:
+        return self.engine.n_segments
+
+    def _arm_latch(self, mask: Optional[torch.Tensor]):
+        if not self.latch_first_action:
+            return
+        ts = self.engine["t_servo"]
+        if mask is None:
+            ts.fill_(self.servo_interval)
+        else:
+            ts[mask.to(self.device).bool()] = self.servo_interval
+
+    def reset(self, *, seed: Optional[int] = None, mask: Optional[torch.Tensor] = None, options=None):
+        """Fresh-env state for all envs (or the masked ones).  A seed re-keys the Philox streams."""
+        if seed is not None:
+            self.engine.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
+        self.engine.reset(mask)
+        self._arm_latch(mask)
+        return self._obs(), {}
+
+    def _stage(self, actions: Dict):
+        gc = actions["generator_control"]
+        self.engine.set_actions(actions["servo"], gc["target_voltage"], gc["current_mode"], gc["ON_time"], gc["OFF_time"])
+
+    def _obs(self) -> Dict[str, torch.Tensor]:
+        o = self.engine.observe()
+        return {k: o[i] for i, k in enumerate(OBS_KEYS)}
+
+    def step(self, actions: Dict, n_us: Optional[int] = None, draws: Optional[torch.Tensor] = None):
+        """Advance every env by `n_us` µs (default: one control step).  Returns the Gymnasium
+        5-tuple with batched tensors: obs dict of [n_envs] float32, reward [n_envs] (0.0 — the
+        reference's reward is a placeholder, wire_edm.py:185-187), terminated, truncated, info."""
+        n_us = self.servo_interval if n_us is None else int(n_us)
+        self._stage(actions)
+        self.engine.step(n_us, draws)
+        obs = self._obs()
+        flags = self.engine["flags"]
+        terminated = (flags & N.F_DONE) != 0
+        info = {
+            "wire_broken": (flags & N.F_BROKEN) != 0,
+            "target_reached": (flags & N.F_TARGET) != 0,
+            "mode_error": (flags & N.F_MODE_ERROR) != 0,
+            "spark_state": self.engine["spark_state"],
+            "time": self.engine["time"],
+            "control_step": True,
+        }
+        reward = torch.zeros(self.n_envs, dtype=torch.float32, device=self.device)
+        truncated = torch.zeros(self.n_envs, dtype=torch.bool, device=self.device)
+        if self.auto_reset:
+            info["final_terminated"] = terminated.clone()
+            self.engine.reset(terminated)
+            self._arm_latch(terminated)
+        return obs, reward, terminated, truncated, info
+
+    def step_host(self, n_us: Optional[int] = None) -> torch.Tensor:
+        """Host-buffer control step through `sparc_step_host`: fill `self.engine.host_actions`
+        (pinned) first; returns the pinned [8, n_envs] observation array."""
+        return self.engine.step_host(self.servo_interval if n_us is None else int(n_us))
+
+    def check_mode_errors(self) -> None:
+        """Raise the reference's ValueError (material.py:108-113) if any env sparked with a current
+        mode that has no crater data."""
+        bad = ((self.engine["flags"] & N.F_MODE_ERROR) != 0).nonzero().flatten()
+        if bad.numel():
+            m = int(self.engine["current_mode"][bad[0]].item())
+            avail = [f"I{k}" for k in self._valid_modes]
+            raise ValueError(f"Current mode I{max(m, 0)} is not available in crater data. Available modes: {avail}")
+
+    def episode_stats(self, all_reduce: bool = True) -> Dict[str, float]:
+        """Episode statistics summed over envs; all-reduced over ranks (NCCL) when
+        torch.distributed is initialised — the only collective on this path."""
+        st = self.engine.reduce_stats().clone()
+        if all_reduce and torch.distributed.is_available() and torch.distributed.is_initialized():
+            torch.distributed.all_reduce(st)
+        v = st.cpu().tolist()
+        keys = ("sparks", "short_us", "short_events", "crater_um3", "short_pulses", "env_us", "broken", "target_reached")
+        return dict(zip(keys, v))
+
+    # convenience views of the live SoA state (zero-copy device tensors)
+    @property
+    def wire_temperature(self) -> torch.Tensor:
+        return self.engine.T
+
+    def state_tensor(self, name: str) -> torch.Tensor:
+        return self.engine[name]
+
+    @staticmethod
+    def constant_action(servo=0.0, target_voltage=80.0, current_mode=5, ON_time=3.0, OFF_time=80.0) -> Dict:
+        return {"servo": np.float32(servo),
+                "generator_control": {"target_voltage": np.float32(target_voltage), "current_mode": np.int32(current_mode),
+                                      "ON_time": np.float32(ON_time), "OFF_time": np.float32(OFF_time)}}

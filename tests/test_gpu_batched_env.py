@@ -1,0 +1,112 @@
+"""The vectorised surface on the GPU: API shapes, controllers on device, auto-reset,
+GPU-count invariance of the Philox streams, statistics against the running reference."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_DIR
+
+pytestmark = pytest.mark.gpu
+
+README = dict(workpiece_height=15.0, wire_diameter=0.25, wire_material="brass", target_cutting_distance=800.0)
+
+
+def _env(n, **kw):
+    from sparc_b200 import BatchedWireEDMEnv, EnvironmentConfig
+
+    cfg = kw.pop("config", README)
+    return BatchedWireEDMEnv(n, config=EnvironmentConfig(**cfg), **kw)
+
+
+def test_batched_api_shapes_and_gap_controller():
+    """BASELINE cfg 3 flavour: position mode, proportional gap controller evaluated on device."""
+    import torch
+
+    env = _env(512, seed=5)
+    obs, info = env.reset()
+    assert set(obs) == {"gap", "wire_velocity", "mean_voltage", "sparks", "short_us", "max_temperature", "debris_density"}
+    assert obs["gap"].shape == (512,) and torch.all(obs["gap"] == 50.0)
+    for _ in range(60):
+        servo = torch.clamp(0.1 * (obs["gap"] - 25.0), -1.0, 1.0)        # run_simulation.py:28-33 sign
+        act = {"servo": servo, "generator_control": {"target_voltage": 80.0, "current_mode": 5, "ON_time": 3.0, "OFF_time": 80.0}}
+        obs, rew, term, trunc, info = env.step(act)
+    assert rew.shape == (512,) and term.dtype == torch.bool and not trunc.any()
+    assert int(info["time"][0]) == 60000 and not term.any()
+    g = obs["gap"].mean().item()
+    assert 25.0 < g < 45.0, g                      # the stabilising controller closes the gap
+    st = env.episode_stats()
+    assert st["env_us"] == 512 * 60000 and st["sparks"] > 512 * 10
+
+
+def test_streams_do_not_depend_on_sharding():
+    """Global env ids key the Philox streams: 2 shards of 64 == one batch of 128 (cfg 4 invariant)."""
+    import torch
+
+    a = _env(128, seed=11)
+    b0 = _env(64, seed=11, env_id_base=0)
+    b1 = _env(64, seed=11, env_id_base=64)
+    act = a.constant_action(servo=0.1)
+    for _ in range(6):
+        a.step(act); b0.step(act); b1.step(act)
+    for name in ("wp", "wire", "v", "debris_volume", "time", "spark_state", "stat_sparks"):
+        whole = a.state_tensor(name)
+        parts = torch.cat([b0.state_tensor(name), b1.state_tensor(name)])
+        assert torch.equal(whole, parts), name
+    assert torch.equal(a.wire_temperature, torch.cat([b0.wire_temperature, b1.wire_temperature]))
+    assert a.state_tensor("stat_sparks").sum() > 0
+
+
+def test_auto_reset_and_first_latch():
+    import torch
+
+    env = _env(64, config=dict(README, initial_gap=10.0, target_cutting_distance=10.004), seed=3, auto_reset=True)
+    act = env.constant_action(servo=0.0, OFF_time=20.0)
+    seen = torch.zeros(64, dtype=torch.bool, device=env.device)
+    for _ in range(40):
+        obs, rew, term, trunc, info = env.step(act)
+        seen |= info["final_terminated"]
+        # a reset env is fresh again: time 0, latch armed
+        if info["final_terminated"].any():
+            i = int(info["final_terminated"].nonzero()[0])
+            assert int(env.state_tensor("time")[i]) == 0 and int(env.state_tensor("episode")[i]) >= 1
+    assert seen.float().mean() > 0.9
+    # latch_first_action: the very first control step already runs on the action's generator settings
+    env2 = _env(4, seed=1)
+    env2.step(env2.constant_action(target_voltage=123.0))
+    assert torch.all(env2.state_tensor("target_voltage") == 123.0)
+    env3 = _env(4, seed=1, latch_first_action=False)        # reference quirk: first ms on defaults
+    env3.step(env3.constant_action(target_voltage=123.0))
+    assert torch.all(env3.state_tensor("target_voltage") == 0.0)
+
+
+def test_statistics_match_running_reference():
+    """On-device RNG: spark rate and removal per env must agree with the unmodified reference
+    (tests/golden/stats_reference.json) within a 99.9 % confidence interval (|z| < 3.29)."""
+    ref = json.load(open(os.path.join(GOLDEN_DIR, "stats_reference.json")))
+    n = 4096
+    env = _env(n, seed=2026, latch_first_action=False)      # same protocol as the reference runs
+    act = env.constant_action(servo=np.float32(0.1))
+    for _ in range(50):
+        env.step(act)
+    sparks = env.state_tensor("stat_sparks").double().cpu().numpy()
+    removed = (env.state_tensor("wp").double().cpu().numpy() - 50.0)
+    for name, gpu, key in (("sparks", sparks, "sparks"), ("removed_um", removed, "removed_um")):
+        r = np.array([x[key] for x in ref["cfg2"]], dtype=np.float64)
+        z = (gpu.mean() - r.mean()) / np.sqrt(gpu.var(ddof=1) / len(gpu) + r.var(ddof=1) / len(r))
+        print(f"\n{name}: gpu {gpu.mean():.4f} ref {r.mean():.4f} z {z:+.2f}")
+        assert abs(z) < 3.29, (name, gpu.mean(), r.mean(), z)
+    # wire-break statistics: aggressive generator, every env breaks; compare time to break
+    hot = _env(n, config=dict(README, initial_gap=12.0), seed=77, latch_first_action=False)
+    act = hot.constant_action(servo=0.0, target_voltage=100.0, current_mode=17, ON_time=5.0, OFF_time=6.0)
+    for _ in range(30):
+        hot.step(act)
+    steps = hot.state_tensor("stat_steps").double().cpu().numpy()
+    broken = ((hot.state_tensor("flags") & 2) != 0).double().cpu().numpy()
+    r_steps = np.array([x["steps"] for x in ref["hot"]], dtype=np.float64)
+    r_broken = np.array([x["broken"] for x in ref["hot"]], dtype=np.float64)
+    z = (steps.mean() - r_steps.mean()) / np.sqrt(steps.var(ddof=1) / n + r_steps.var(ddof=1) / len(r_steps))
+    print(f"\nbreak: gpu P {broken.mean():.3f} mean t {steps.mean():.0f} us; ref P {r_broken.mean():.3f} mean t {r_steps.mean():.0f} us; z {z:+.2f}")
+    assert abs(broken.mean() - r_broken.mean()) < 0.05
+    assert abs(z) < 3.29
