@@ -13,6 +13,7 @@
 #include "../../include/sparc_b200.h"
 #include "state_layout.h"
 #include "step_kernel.cuh"
+#include "step_kernel2.cuh"
 
 namespace {
 
@@ -172,15 +173,25 @@ using StepFn = void (*)(const SparcParams, const SparcStatePtrs, const sparc::St
 
 struct Variant {
     int K, L;
-    StepFn fn[2];   // [INJECT]
+    StepFn fn[2];    // [INJECT]  per-µs scalar path (step_kernel.cuh)
+    StepFn fn2[2];   // [INJECT]  look-ahead organisation (step_kernel2.cuh), L == 32 only
 };
 
-#define VARIANT(K, L) {K, L, {sparc::step_kernel<K, L, false>, sparc::step_kernel<K, L, true>}}
+#define VARIANT32(K) {K, 32, {sparc::step_kernel<K, 32, false>, sparc::step_kernel<K, 32, true>}, \
+                      {sparc::step_kernel2<K, false>, sparc::step_kernel2<K, true>}}
+#define VARIANT16(K) {K, 16, {sparc::step_kernel<K, 16, false>, sparc::step_kernel<K, 16, true>}, {nullptr, nullptr}}
 const Variant kVariants[] = {
-    VARIANT(4, 32), VARIANT(8, 32), VARIANT(12, 32), VARIANT(13, 32), VARIANT(16, 32),
-    VARIANT(20, 32), VARIANT(24, 32), VARIANT(28, 32), VARIANT(36, 32),
-    VARIANT(24, 16), VARIANT(26, 16),
+    VARIANT32(4), VARIANT32(8), VARIANT32(12), VARIANT32(13), VARIANT32(16),
+    VARIANT32(20), VARIANT32(24), VARIANT32(28), VARIANT32(36),
+    VARIANT16(24), VARIANT16(26),
 };
+
+// SPARC_KERNEL=1 selects the per-µs kernel (A/B experiments); default is the look-ahead kernel
+bool use_lookahead()
+{
+    const char *s = getenv("SPARC_KERNEL");
+    return !(s && atoi(s) == 1);
+}
 constexpr int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
 
 const Variant *pick_variant(int n_segments)
@@ -236,7 +247,9 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     int warps = (n_envs + G - 1) / G;
     int wpb = SPARC_BLOCK_THREADS / 32;
     int blocks = (warps + wpb - 1) / wpb;
-    v->fn[draws ? 1 : 0]<<<blocks, SPARC_BLOCK_THREADS, 0, (cudaStream_t)stream>>>(*p, S, a);
+    StepFn fn = v->fn[draws ? 1 : 0];
+    if (v->fn2[0] && use_lookahead()) fn = v->fn2[draws ? 1 : 0];
+    fn<<<blocks, SPARC_BLOCK_THREADS, 0, (cudaStream_t)stream>>>(*p, S, a);
     CUDA_TRY(cudaGetLastError());
     return SPARC_OK;
 }

@@ -133,6 +133,8 @@ struct EnvState {
     int e, it;
     uint32_t env_id, episode;
     bool writer;
+    // ---- mechanics state at the start of the current look-ahead block (step_kernel2.cuh) ----
+    double blk_wire, blk_v, blk_pa;
 };
 
 // generator settings as the ignition module sees them (ignition.py:329-343, 98-113): `x or

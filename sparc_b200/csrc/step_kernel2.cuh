@@ -1,0 +1,548 @@
+// step_kernel2.cuh — fused step kernel, "look-ahead" organisation (sm_100a).
+//
+// Same mapping as step_kernel.cuh (one warp per environment, the wire temperature field in
+// registers, K cells per lane, halos by warp shuffle) and the same general µs (general_pre), but
+// the per-µs scalar state machines no longer run on every µs:
+//
+//   * MECHANICS (mechanics.py:79-114) depends on nothing but the latched servo command, so it is
+//     advanced one BLOCK of <= 32 µs ahead of everything else (exact sequential fp64, identical
+//     operations); the 32 wire positions go to shared memory and from there one per lane.
+//   * LOOK-AHEAD: lane l then evaluates, for µs l of the block, every condition under which the
+//     reference's step() is "quiet" (idle/rest, no latch, no short circuit, no ignition, no
+//     hysteresis refresh, no collision, no zone-mean sample).  The ignition roll is evaluated
+//     here too: lane l computes the Philox word of its own µs.  One ballot gives the length n of
+//     the quiet run.
+//   * QUIET RUN: n µs of pure stencil — no scalar instruction in the loop.  When the wire is
+//     provably cold (max T < critical-1 K and the update is a convex combination, so the maximum
+//     cannot grow without a heat source) even the max/break test is skipped.
+//   * everything else takes the exact general µs (general_pre + heated stencil + break test +
+//     termination), one µs at a time.
+//
+// Every shortcut is conservative: a µs that is not provably quiet runs the general path, which is
+// the reference's logic statement by statement, so results are identical to step_kernel.cuh.
+#pragma once
+#include "step_kernel.cuh"
+
+namespace sparc {
+
+// MechanicsModule.update (mechanics.py:79-114), one µs.
+__device__ __forceinline__ void mech_step(const SparcParams &P, double &wire, double &v, double &prev_accel,
+                                          const double target_delta)
+{
+    double a_nom;
+    if (P.control_mode == 0) {
+        double x_err = wire - (wire + target_delta);
+        a_nom = P.damping_coeff * v + P.stiffness_coeff * x_err;
+    } else {
+        a_nom = -P.omega_n * (v - target_delta);
+    }
+    double da = a_nom - prev_accel;
+    if (fabs(a_nom) <= P.max_acceleration && fabs(da) <= P.max_jerk_dt) {
+        prev_accel = prev_accel + da;           // no clip active
+    } else {
+        if (a_nom > P.max_acceleration) a_nom = P.max_acceleration;
+        else if (a_nom < -P.max_acceleration) a_nom = -P.max_acceleration;
+        da = a_nom - prev_accel;
+        if (da > P.max_jerk_dt) da = P.max_jerk_dt;
+        else if (da < -P.max_jerk_dt) da = -P.max_jerk_dt;
+        prev_accel = prev_accel + da;
+    }
+    v += prev_accel * P.mech_dt;
+    if (!(fabs(v) <= P.max_speed)) {
+        if (v > P.max_speed) v = P.max_speed;
+        else if (v < -P.max_speed) v = -P.max_speed;
+    }
+    wire += v * P.mech_dt;
+}
+
+// nb µs of mechanics assuming no acceleration / jerk / speed clip is active (then the update is
+// the same operation sequence as mech_step without its branches).  Returns false if any clip
+// condition was met on any µs: the caller redoes the block with mech_step.
+__device__ __forceinline__ bool mech_block_noclip(const SparcParams &P, double &wire, double &v, double &prev_accel,
+                                                  const double target_delta, const int nb, double *post_s,
+                                                  const bool writer)
+{
+    const double dt = P.mech_dt;
+    bool bad = false;
+    if (P.control_mode == 0) {
+        const double c1 = P.damping_coeff, c2 = P.stiffness_coeff;
+#pragma unroll 4
+        for (int k = 0; k < nb; k++) {
+            const double x_err = wire - (wire + target_delta);
+            const double a_nom = c1 * v + c2 * x_err;
+            const double da = a_nom - prev_accel;
+            bad = bad || !(fabs(a_nom) <= P.max_acceleration) || !(fabs(da) <= P.max_jerk_dt);
+            prev_accel = prev_accel + da;
+            v += prev_accel * dt;
+            bad = bad || !(fabs(v) <= P.max_speed);
+            wire += v * dt;
+            if (writer) post_s[k] = wire;
+        }
+    } else {
+        const double nw = -P.omega_n;
+#pragma unroll 4
+        for (int k = 0; k < nb; k++) {
+            const double a_nom = nw * (v - target_delta);
+            const double da = a_nom - prev_accel;
+            bad = bad || !(fabs(a_nom) <= P.max_acceleration) || !(fabs(da) <= P.max_jerk_dt);
+            prev_accel = prev_accel + da;
+            v += prev_accel * dt;
+            bad = bad || !(fabs(v) <= P.max_speed);
+            wire += v * dt;
+            if (writer) post_s[k] = wire;
+        }
+    }
+    return !bad;
+}
+
+// n quiet µs of compute_thermal_update (wire.py:58-123) without heat sources.  HOT additionally
+// runs _check_wire_breaking (wire.py:376-388) every µs and returns the number of µs executed
+// (n, or j+1 when the wire broke on µs j; `broke` says which).
+template <int K, bool HOT>
+__device__ __forceinline__ int run_quiet(float (&T)[K], const float (&cE)[K], const float (&c0)[K],
+                                         const float (&cR)[K], const float ncL, const float spoolf, const int lane,
+                                         const int n, const float crit_T, const float break_T, int &crit_count,
+                                         bool &broke, bool &cold_after)
+{
+    constexpr unsigned FULL = 0xffffffffu;
+    broke = false;
+#pragma unroll 1
+    for (int k = 0; k < n; k++) {
+        float left = __shfl_up_sync(FULL, T[K - 1], 1);
+        const float right = __shfl_down_sync(FULL, T[0], 1);
+        if (lane == 0) left = spoolf;
+        float dprev = T[0] - left;
+        float lmax = spoolf;
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+            const float dnext = ((j + 1 < K) ? T[j + 1] : right) - T[j];
+            float q = fmaf(cE[j], T[j], c0[j]);
+            q = fmaf(cR[j], dnext, q);
+            q = fmaf(ncL, dprev, q);
+            dprev = dnext;
+            T[j] = T[j] + q;
+            if (HOT) lmax = fmaxf(lmax, T[j]);
+        }
+        if (HOT) {
+            const bool hot = __any_sync(FULL, lmax > crit_T);
+            crit_count = hot ? crit_count + 1 : 0;
+            if (hot && __any_sync(FULL, lmax > break_T)) { broke = true; return k + 1; }
+            if (k == n - 1) cold_after = !__any_sync(FULL, lmax > crit_T - 1.0f);
+        }
+    }
+    if (!HOT) crit_count = 0;
+    return n;
+}
+
+// resident blocks per SM the register budget is sized for
+#ifndef SPARC2_MINB_SMALL
+#define SPARC2_MINB_SMALL 4
+#endif
+constexpr int min_blocks2_for(int K) { return K <= 13 ? SPARC2_MINB_SMALL : (K <= 20 ? 3 : 2); }
+
+#define SPARC_LN2_UP 0.6931471805599460    /* ln2*(1+2^-50): u3 < fl(ln2/den) implies u3*den <= this */
+
+template <int K, bool INJECT>
+__global__ void __launch_bounds__(SPARC_BLOCK_THREADS, min_blocks2_for(K))
+step_kernel2(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
+             const __grid_constant__ StepArgs a)
+{
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int WPB = SPARC_BLOCK_THREADS / 32;
+    __shared__ double sm_post[WPB][32];
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    const int e = blockIdx.x * WPB + wib;
+    if (e >= a.n_envs) return;                  // whole warp; no block-level barrier is used
+    double *post_s = sm_post[wib];
+    const uint32_t k0 = (uint32_t)a.seed, k1 = (uint32_t)(a.seed >> 32);
+
+    // ---------------- load ---------------------------------------------------------------------
+    EnvState s;
+    s.e = e; s.it = 0; s.writer = lane == 0;
+    s.env_id = a.env_id_base + (uint32_t)e;
+    s.episode = (uint32_t)S.episode[e];
+    s.debris_density = S.debris_density[e]; s.flow = S.flow[e];
+    s.d_last_gap = S.d_last_gap[e]; s.d_last_density = S.d_last_density[e];
+    s.w_last_flow = S.w_last_flow[e];
+    s.rand_short_rem = S.rand_short_rem[e]; s.deb_short_rem = S.deb_short_rem[e];
+    s.current_mode = S.current_mode[e];
+    s.win_sparks = 0; s.win_short_us = 0;
+    s.dens_valid = true; s.pend_flush = false; s.fast_ok = false;
+    s.tsi_prev = 0; s.plasma_idx = -1;
+    s.heat_on = false; s.thermal = false; s.refresh = false; s.freeze = false; s.became_done = false;
+    s.jA = 0.f; s.jB = 0.f; s.fP = 0.f; s.hb = 0.f; s.he = 0.f;
+    s.gap_lo_f = 0.0; s.gap_hi_f = -1.0; s.lo_c = 0.0; s.hi_c = 0.0; s.flush_amt = 0.0; s.onoff_thr = 0;
+    derive_generator(s, P, S.target_voltage[e], S.on_time[e], S.off_time[e]);
+
+    double wp = S.wp[e], wire = S.wire[e], v = S.v[e], prev_accel = S.prev_accel[e];
+    double target_delta = S.target_delta[e], voltage = S.voltage[e], debris_volume = S.debris_volume[e];
+    double win_vsum = 0.0, gap_prev = wp - wire;
+    int time = S.time[e], spark_state = S.spark_state[e], spark_dur = S.spark_dur[e], flags = S.flags[e];
+    int crit_count = S.crit_count[e];
+    int w_zone_counter = S.w_zone_counter[e];
+    const int time0 = time;
+    s.latch_time = time - S.t_servo[e];
+    s.tse_ref = time - S.t_spark_end[e];
+    s.ion_end = time + S.ion_rem[e];
+    if (spark_state == 1 && (flags & SPARC_F_HAS_Y))
+        s.plasma_idx = (P.segment_len != 0.0) ? P.zone_start + (int)py_floordiv(S.spark_y[e], P.segment_len) : P.zone_start;
+
+    if (flags & SPARC_F_DONE) {                 // terminated envs are left untouched
+        if (s.writer) { S.win_vsum[e] = 0.0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0; }
+        return;
+    }
+
+    int next_latch = s.latch_time + P.servo_interval;
+    bool fast_ok = false, ran_fast = false, zone_mean_written = false, done = false;
+    int tsi_break = -1;
+
+    // upper bound of lambda(gap) = ln2/(a g^2 + b g + c) over all gaps (ignition.py:348-364): a
+    // draw above it can never ignite, whatever the gap.
+    double lam_bound = 2.0;
+    if (P.ignition_a_coeff > 0.0) {
+        double den_min = P.ignition_c_coeff - P.ignition_b_coeff * P.ignition_b_coeff / (4.0 * P.ignition_a_coeff);
+        if (den_min > 0.0) lam_bound = 0.6931471805599453 / den_min * (1.0 + 1e-9);
+    }
+    uint32_t w_thresh = 0xffffffffu;            // word >= w_thresh  =>  u01(word) >= lam_bound
+    if (lam_bound < 0.999) w_thresh = (uint32_t)(lam_bound * 4294967296.0) + 2u;
+
+    // ---------------- temperature field -> registers -----------------------------------------
+    const int N = P.n_segments;
+    const int M = N - 1;                        // dynamic cells 1..N-1; cell 0 == spool_T
+    float spoolf = (float)P.spool_T;
+    asm volatile("" : "+f"(spoolf));            // keep it in a register (no per-µs F2F rematerialisation)
+    float T[K];
+    float *Trow = S.T + (size_t)e * S.n_pad;
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+        int sl = lane * K + j;
+        T[j] = (sl < M) ? Trow[sl + 1] : spoolf;
+    }
+
+    // ---------------- stencil coefficients ---------------------------------------------------
+    const double f = P.temp_update_factor;
+    float cRf, ncL;
+    {
+        const double unwind_v = S.unwind_v[e];
+        double adv = 0.0;                       // wire.py:299-309
+        if (fabs(unwind_v) > 1e-6) adv = P.density_times_cp * fabs(unwind_v) * P.S;
+        if (!(fabs(adv) > 1e-9)) adv = 0.0;     // wire.py:114
+        cRf = (float)(f * P.k_cond_coeff);
+        ncL = -(float)(f * (P.k_cond_coeff + adv));
+    }
+    float cE[K], c0[K], cR[K];
+    bool convex = false;                        // T' is a convex combination of T, T_diel (no source)
+    auto refresh_coeffs = [&](float hb, float he) {
+#pragma unroll
+        for (int j = 0; j < K; j++) {
+            int sl = lane * K + j;
+            int i = sl + 1;
+            if (sl < M) {
+                float h = (i >= P.actual_zone_start && i < P.actual_zone_end) ? he : hb;
+                double hA = (double)h * P.A;    // conv_coeff, wire.py:110
+                cE[j] = (float)(-(f * hA));
+                c0[j] = (float)(f * hA * P.dielectric_temperature);
+                cR[j] = (i < N - 1) ? cRf : 0.0f;     // Neumann end, wire.py:95
+            } else {                            // pad slot: pinned near spool_T, feeds nothing
+                cE[j] = -1.0f;
+                c0[j] = spoolf;
+                cR[j] = 0.0f;
+            }
+        }
+        const float hmax = fmaxf(hb, he), hmin = fminf(hb, he);
+        const float ce_max = (float)(f * ((double)hmax * P.A));
+        convex = hmin >= 0.0f && cRf >= 0.0f && ncL <= 0.0f && (cRf - ncL + ce_max) <= 0.999f &&
+                 fmaxf((float)P.dielectric_temperature, spoolf) < P.critical_temperature_f32 - 1.0f;
+    };
+    refresh_coeffs(S.h_base[e], S.h_enh[e]);
+    bool cold_ok = false;                       // max T < critical - 1 K after the last executed µs
+
+    // contact span in slot coordinates of this lane
+    const int j_span_lo = P.contact_bottom_idx - 1 - lane * K;
+    const int j_span_hi = P.contact_top_idx - 1 - lane * K;
+    const double *drow = INJECT ? a.draws + (size_t)e * a.n_us * SPARC_N_DRAW_SLOTS : nullptr;
+
+    int it = 0;
+    while (it < a.n_us && !done) {
+        // ================= block setup: mechanics look-ahead ==================================
+        int nb = a.n_us - it;
+        if (nb > 32) nb = 32;
+        int to_latch = next_latch - time;
+        double delta_blk = target_delta;
+        bool force_general = false;
+        if (to_latch <= 0) {                    // the first µs of this block latches the action
+            delta_blk = (double)a.act.servo[e];
+            to_latch = (P.servo_interval > 1) ? P.servo_interval : 1;
+            force_general = true;
+        }
+        if (nb > to_latch) nb = to_latch;       // a block never straddles a latch
+        const double wire_b = wire;
+        s.blk_wire = wire; s.blk_v = v; s.blk_pa = prev_accel;
+        __syncwarp();
+        if (!mech_block_noclip(P, wire, v, prev_accel, delta_blk, nb, post_s, lane == 0)) {
+            wire = s.blk_wire; v = s.blk_v; prev_accel = s.blk_pa;     // a clip was active: exact path
+#pragma unroll 1
+            for (int k = 0; k < nb; k++) {
+                mech_step(P, wire, v, prev_accel, delta_blk);
+                if (lane == 0) post_s[k] = wire;
+            }
+        }
+        __syncwarp();
+        const double post_l = post_s[(lane < nb) ? lane : nb - 1];      // wire after µs `lane`
+        double pre_l = __shfl_up_sync(FULL, post_l, 1);                  // wire before µs `lane`
+        if (lane == 0) pre_l = wire_b;
+        // ignition roll of µs `lane` (slot 2): word (time+lane)&3 of Philox block (time+lane)>>2
+        uint32_t w_l = 0;
+        if (!INJECT) {
+            const uint32_t tl = (uint32_t)(time + lane);
+            uint32_t w[4];
+            philox4x32_10(s.env_id, tl >> 2, s.episode, 2u, k0, k1, w);
+            w_l = pick4(w, tl & 3);
+        }
+        // finished inside this block: exact mechanics state after `steps` µs of it
+        auto rewind_mech = [&](int steps) {
+            wire = s.blk_wire; v = s.blk_v; prev_accel = s.blk_pa;
+#pragma unroll 1
+            for (int k = 0; k < steps; k++) mech_step(P, wire, v, prev_accel, delta_blk);
+        };
+
+        int i = 0;
+        while (i < nb) {
+            // ================= look-ahead: length of the quiet run starting at µs i ===========
+            int n = 0;
+            int off_tr = -1;                    // run offset of the rest -> idle transition µs
+            const double g = wp - pre_l;
+            if (!force_general && fast_ok && (spark_state == 0 || spark_state == -2)) {
+                const int off = lane - i;
+                bool ok = lane < nb && g >= s.gap_lo_f && g <= s.gap_hi_f;
+                // debris after at most off+1 deferred flushes (sequential rounding <= 32 ulp(1))
+                double deb_lo = debris_volume;
+                if (debris_volume > 0.001) deb_lo = debris_volume - (double)(off + 1) * s.flush_amt - 1e-14;
+                ok = ok && deb_lo >= s.lo_c * g && debris_volume <= s.hi_c * g;
+                ok = ok && !(post_l > wp + 100.0);              // collision µs (wire_edm.py:173-175)
+                if (spark_state == -2) {
+                    off_tr = s.onoff_thr - spark_dur - 1;
+                    if (off_tr < 0) off_tr = 0;
+                }
+                if (P.compute_zone_mean) ok = ok && (w_zone_counter + off + 1 < P.zone_mean_interval);
+                if (INJECT) {
+                    if (lane < nb) {
+                        const double *d = drow + (size_t)(it + lane) * SPARC_N_DRAW_SLOTS;
+                        ok = ok && d[0] >= SPARC_U1_SAFE;
+                        if (off > off_tr) {
+                            const double u3 = d[2];
+                            if (!(u3 >= lam_bound)) {
+                                double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
+                                ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
+                            }
+                        }
+                    }
+                } else if (off > off_tr && w_l < w_thresh) {
+                    // u3 < fl(ln2/den) can only hold if u3*den <= ln2*(1+2^-50)
+                    const double u3 = u01(w_l);
+                    double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
+                    ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
+                }
+                const unsigned stop = __ballot_sync(FULL, !ok) >> i;
+                n = stop ? __ffs(stop) - 1 : 32 - i;
+            }
+            force_general = false;
+
+            if (n > 0) {
+                // ================= quiet run ===================================================
+                bool broke = false;
+                int nx;
+                if (cold_ok && convex)
+                    nx = run_quiet<K, false>(T, cE, c0, cR, ncL, spoolf, lane, n, 0.f, 0.f, crit_count, broke, cold_ok);
+                else
+                    nx = run_quiet<K, true>(T, cE, c0, cR, ncL, spoolf, lane, n, P.critical_temperature_f32,
+                                            P.breaking_temperature_f32, crit_count, broke, cold_ok);
+                // scalar bookkeeping of the nx quiet µs (ignition.py:302-319, dielectric.py:104-144)
+                int n_idle = nx;
+                if (spark_state == -2) {
+                    if (nx > off_tr) {          // rest -> idle on run offset off_tr
+                        spark_state = 0; spark_dur = 0; flags &= ~SPARC_F_HAS_Y;
+                        if (s.writer) S.spark_y[e] = -1.0;
+                        n_idle = nx - off_tr;
+                    } else { spark_dur += nx; n_idle = 0; }
+                }
+                voltage = (n_idle > 0) ? s.tv_eff : 0.0;
+                win_vsum += (double)n_idle * s.tv_eff;
+                if (debris_volume > 0.001 && s.flush_amt > 0.0) {
+#pragma unroll 1
+                    for (int k = 0; k < nx && debris_volume > 0.001; k++) debris_volume = debris_volume - s.flush_amt;
+                }
+                gap_prev = __shfl_sync(FULL, g, i + nx - 1);
+                ran_fast = true;
+                if (P.compute_zone_mean) w_zone_counter += nx;
+                if (broke) {                    // wire_edm.py:129-130 on the last µs of the run
+                    flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
+                    tsi_break = 0;
+                    done = true;
+                    time += nx - 1;
+                    rewind_mech(i + nx - 1);
+                    break;
+                }
+                time += nx;
+                i += nx;
+                continue;
+            }
+
+            // ================= general µs ======================================================
+            s.wp = wp; s.wire = __shfl_sync(FULL, pre_l, i); s.v = 0.0; s.prev_accel = 0.0;
+            s.target_delta = target_delta;
+            s.voltage = voltage; s.debris_volume = debris_volume; s.win_vsum = win_vsum; s.gap_prev = gap_prev;
+            s.time = time; s.spark_state = spark_state; s.spark_dur = spark_dur; s.flags = flags;
+            s.it = it + i;
+            if (ran_fast) { s.dens_valid = false; s.pend_flush = true; ran_fast = false; }
+            general_pre<INJECT>(s, P, S, a);
+            wp = s.wp; target_delta = s.target_delta; voltage = s.voltage; debris_volume = s.debris_volume;
+            win_vsum = s.win_vsum; gap_prev = s.gap_prev;
+            spark_state = s.spark_state; spark_dur = s.spark_dur; flags = s.flags;
+            next_latch = s.latch_time + P.servo_interval;
+            fast_ok = s.fast_ok;
+            if (s.refresh) refresh_coeffs(s.hb, s.he);
+            if (s.freeze) {                     // crater-table miss: frozen before the thermal update
+                done = true;
+                rewind_mech(i);
+                break;
+            }
+            // ---- compute_thermal_update with sources (wire.py:58-123) -------------------------
+            float lmax = spoolf;
+            {
+                float left = __shfl_up_sync(FULL, T[K - 1], 1);
+                const float right = __shfl_down_sync(FULL, T[0], 1);
+                if (lane == 0) left = spoolf;
+                float acc[K];
+#pragma unroll
+                for (int j = 0; j < K; j++) acc[j] = fmaf(cE[j], T[j], c0[j]);
+                if (s.heat_on) {
+                    const float jA = s.jA, jB = s.jB, fP = s.fP;
+                    const int jp = (s.spark_state == 1 && s.plasma_idx >= 0 && s.plasma_idx < N)
+                                       ? s.plasma_idx - 1 - lane * K : -(1 << 20);
+#pragma unroll
+                    for (int j = 0; j < K; j++) {
+                        if (j >= j_span_lo && j <= j_span_hi) acc[j] += fmaf(jA, T[j], jB);
+                        if (j == jp) acc[j] += fP;
+                    }
+                }
+                float dprev = T[0] - left;
+#pragma unroll
+                for (int j = 0; j < K; j++) {
+                    const float dnext = ((j + 1 < K) ? T[j + 1] : right) - T[j];
+                    float q = fmaf(cR[j], dnext, acc[j]);
+                    q = fmaf(ncL, dprev, q);
+                    dprev = dnext;
+                    T[j] = T[j] + q;
+                    lmax = fmaxf(lmax, T[j]);
+                }
+            }
+            // ---- _check_wire_breaking (wire.py:376-388) ---------------------------------------
+            cold_ok = !__any_sync(FULL, lmax > P.critical_temperature_f32 - 1.0f);
+            bool hot = false, brk = false;
+            if (!cold_ok) {
+                hot = __any_sync(FULL, lmax > P.critical_temperature_f32);
+                if (hot) brk = __any_sync(FULL, lmax > P.breaking_temperature_f32);
+            }
+            crit_count = hot ? crit_count + 1 : 0;
+            // zone mean (wire.py:338-347, 390-394), only when enabled
+            if (P.compute_zone_mean) {
+                w_zone_counter += 1;
+                if (w_zone_counter >= P.zone_mean_interval) {
+                    int za = P.actual_zone_start, zb = P.actual_zone_end;
+                    if (!(zb > za && zb <= N)) { za = 0; zb = N; }
+                    float part = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < K; j++) {
+                        int c = lane * K + j + 1;
+                        if (c >= za && c < zb) part += T[j];
+                    }
+                    if (lane == 0 && za == 0) part += spoolf;    // cell 0 when the zone starts at 0
+                    double tot = (double)part;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(FULL, tot, o);
+                    double zm = (double)(float)(tot / (double)(zb - za));
+                    if (s.writer) { S.w_last_zone_mean[e] = zm; S.wire_avg_T[e] = zm; }
+                    zone_mean_written = true;
+                    w_zone_counter = 0;
+                }
+            }
+            if (brk) {
+                // wire_edm.py:129-130: early return, no mechanics, no time bookkeeping
+                flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
+                tsi_break = s.tsi_prev;
+                done = true;
+                rewind_mech(i);
+                break;
+            }
+            // mechanics of this µs is post_l of lane i; time bookkeeping (wire_edm.py:134-144)
+            time += 1;
+            if (spark_state == 1) s.tse_ref = time;
+            // ---- _check_termination (wire_edm.py:172-179) -------------------------------------
+            const double wire_after = __shfl_sync(FULL, post_l, i);
+            if (wire_after > wp + 100.0) { flags |= SPARC_F_BROKEN; done = true; }
+            else if (wp >= P.target_position) { flags |= SPARC_F_TARGET; done = true; }
+            if (done) { rewind_mech(i + 1); break; }
+            i += 1;
+        }
+        it += nb;
+    }
+
+    // ---------------- store ------------------------------------------------------------------
+#pragma unroll
+    for (int j = 0; j < K; j++) {
+        int sl = lane * K + j;
+        if (sl < M) Trow[sl + 1] = T[j];
+    }
+    if (lane == 0) {
+        const bool thermal_break = (flags & SPARC_F_THERMAL_BREAK) != 0 && tsi_break >= 0;   // broke in THIS call
+        const int win_steps = (time - time0) + (thermal_break ? 1 : 0);
+        if (win_steps > 0 || (flags & SPARC_F_MODE_ERROR)) {
+            // bring the lazily kept dielectric state to what the reference holds after its last µs
+            s.debris_volume = debris_volume; s.gap_prev = gap_prev;
+            if (ran_fast) { s.dens_valid = false; s.pend_flush = true; }
+            materialize(s, P);
+            debris_volume = s.debris_volume;
+        }
+        Trow[0] = spoolf;
+        S.wp[e] = wp; S.wire[e] = wire; S.v[e] = v; S.prev_accel[e] = prev_accel;
+        S.voltage[e] = voltage;
+        S.current[e] = (spark_state == 1 || spark_state == -1) ? s.ipk : 0.0;
+        S.target_delta[e] = target_delta;
+        S.debris_volume[e] = debris_volume; S.debris_density[e] = s.debris_density;
+        if (win_steps > 0) {
+            double gq = (gap_prev > 0.001) ? gap_prev : 0.001;
+            S.cavity_volume[e] = P.cavity_volume_coeff * (gq * 0.001);     // dielectric.py:91-92
+        }
+        S.flow[e] = s.flow;
+        if (!(spark_state == 1 && spark_dur == 0) && win_steps > 0) S.last_crater_volume[e] = 0.0;
+        S.d_last_gap[e] = s.d_last_gap; S.d_last_density[e] = s.d_last_density;
+        S.w_last_flow[e] = s.w_last_flow;
+        if (P.compute_zone_mean && win_steps > 0 && !zone_mean_written) S.wire_avg_T[e] = S.w_last_zone_mean[e];
+        S.win_vsum[e] = win_vsum;
+        S.time[e] = time; S.t_servo[e] = time - s.latch_time; S.t_open_v[e] = time;
+        // time_since_spark_ignition (wire_edm.py:139-144): dur+1 while sparking, else 0; the
+        // µs that returns early (thermal break / mode error) leaves the previous value
+        int tsi = (spark_state == 1) ? spark_dur + 1 : 0;
+        if (thermal_break) tsi = tsi_break;
+        else if (flags & SPARC_F_THERMAL_BREAK) tsi = S.t_spark_ign[e];
+        if (flags & SPARC_F_MODE_ERROR) tsi = 0;
+        S.t_spark_ign[e] = tsi;
+        S.t_spark_end[e] = time - s.tse_ref;
+        S.spark_state[e] = spark_state; S.spark_dur[e] = spark_dur;
+        S.rand_short_rem[e] = s.rand_short_rem; S.deb_short_rem[e] = s.deb_short_rem;
+        {
+            int ir = s.ion_end - time - (thermal_break ? 1 : 0);
+            S.ion_rem[e] = ir > 0 ? ir : 0;
+        }
+        S.crit_count[e] = crit_count;
+        S.current_mode[e] = s.current_mode;
+        S.w_zone_counter[e] = w_zone_counter; S.flags[e] = flags;
+        S.stat_short_us[e] += s.win_short_us;
+        S.stat_steps[e] += win_steps;
+        S.win_sparks[e] = s.win_sparks; S.win_short_us[e] = s.win_short_us; S.win_steps[e] = win_steps;
+    }
+}
+
+}  // namespace sparc
