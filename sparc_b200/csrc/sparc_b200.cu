@@ -181,7 +181,7 @@ struct Variant {
                       {sparc::step_kernel2<K, false>, sparc::step_kernel2<K, true>}}
 #define VARIANT16(K) {K, 16, {sparc::step_kernel<K, 16, false>, sparc::step_kernel<K, 16, true>}, {nullptr, nullptr}}
 const Variant kVariants[] = {
-    VARIANT32(4), VARIANT32(8), VARIANT32(12), VARIANT32(13), VARIANT32(16),
+    VARIANT32(4), VARIANT32(8), VARIANT32(12), VARIANT32(14), VARIANT32(16),
     VARIANT32(20), VARIANT32(24), VARIANT32(28), VARIANT32(36),
     VARIANT16(24), VARIANT16(26),
 };

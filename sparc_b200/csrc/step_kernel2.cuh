@@ -95,33 +95,47 @@ __device__ __forceinline__ bool mech_block_noclip(const SparcParams &P, double &
     return !bad;
 }
 
+// ---- packed stencil ---------------------------------------------------------------------------
+// sm_100 has two-wide fp32 instructions (FFMA2/FADD2, PTX fma.rn.f32x2): one issue slot and one
+// pipe pass for two IEEE-rn operations — measured 1.95 FFMA2 vs 2.1 register-operand FFMA per
+// clock per SM (tools/microbench2.cu).  Lane cells are split in two halves of H = K/2 cells;
+// pair j holds (T[j], T[j+H]) so that neighbour differences of pair j are pair j+1 minus pair j.
+// Element-wise the operation sequence is unchanged: q = fma(cE,T,c0); q = fma(cR,dnext,q);
+// q = fma(ncL,dprev,q); T = T + q.
+__device__ __forceinline__ float2 sub2(const float2 a, const float2 b)
+{
+    return __fadd2_rn(a, make_float2(-b.x, -b.y));
+}
+
 // n quiet µs of compute_thermal_update (wire.py:58-123) without heat sources.  HOT additionally
 // runs _check_wire_breaking (wire.py:376-388) every µs and returns the number of µs executed
 // (n, or j+1 when the wire broke on µs j; `broke` says which).
-template <int K, bool HOT>
-__device__ __forceinline__ int run_quiet(float (&T)[K], const float (&cE)[K], const float (&c0)[K],
-                                         const float (&cR)[K], const float ncL, const float spoolf, const int lane,
+template <int H, bool HOT>
+__device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], const float2 (&c0)[H],
+                                         const float2 (&cR)[H], const float ncL, const float spoolf, const int lane,
                                          const int n, const float crit_T, const float break_T, int &crit_count,
                                          bool &broke, bool &cold_after)
 {
     constexpr unsigned FULL = 0xffffffffu;
+    const float2 ncL2 = make_float2(ncL, ncL);
     broke = false;
 #pragma unroll 1
     for (int k = 0; k < n; k++) {
-        float left = __shfl_up_sync(FULL, T[K - 1], 1);
-        const float right = __shfl_down_sync(FULL, T[0], 1);
+        float left = __shfl_up_sync(FULL, T[H - 1].y, 1);
+        const float right = __shfl_down_sync(FULL, T[0].x, 1);
         if (lane == 0) left = spoolf;
-        float dprev = T[0] - left;
+        float2 dprev = sub2(T[0], make_float2(left, T[H - 1].x));
+        const float2 last_next = make_float2(T[0].y, right);
         float lmax = spoolf;
 #pragma unroll
-        for (int j = 0; j < K; j++) {
-            const float dnext = ((j + 1 < K) ? T[j + 1] : right) - T[j];
-            float q = fmaf(cE[j], T[j], c0[j]);
-            q = fmaf(cR[j], dnext, q);
-            q = fmaf(ncL, dprev, q);
+        for (int j = 0; j < H; j++) {
+            const float2 dnext = sub2((j + 1 < H) ? T[j + 1] : last_next, T[j]);
+            float2 q = __ffma2_rn(cE[j], T[j], c0[j]);
+            q = __ffma2_rn(cR[j], dnext, q);
+            q = __ffma2_rn(ncL2, dprev, q);
             dprev = dnext;
-            T[j] = T[j] + q;
-            if (HOT) lmax = fmaxf(lmax, T[j]);
+            T[j] = __fadd2_rn(T[j], q);
+            if (HOT) lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
         }
         if (HOT) {
             const bool hot = __any_sync(FULL, lmax > crit_T);
@@ -212,12 +226,15 @@ step_kernel2(const __grid_constant__ SparcParams P, const __grid_constant__ Spar
     const int M = N - 1;                        // dynamic cells 1..N-1; cell 0 == spool_T
     float spoolf = (float)P.spool_T;
     asm volatile("" : "+f"(spoolf));            // keep it in a register (no per-µs F2F rematerialisation)
-    float T[K];
+    static_assert(K % 2 == 0, "packed stencil needs an even number of cells per lane");
+    constexpr int H = K / 2;
+    float2 T[H];                                // T[j] = (cell j, cell j+H) of this lane's K slots
     float *Trow = S.T + (size_t)e * S.n_pad;
 #pragma unroll
-    for (int j = 0; j < K; j++) {
-        int sl = lane * K + j;
-        T[j] = (sl < M) ? Trow[sl + 1] : spoolf;
+    for (int j = 0; j < H; j++) {
+        const int sa = lane * K + j, sb = sa + H;
+        T[j].x = (sa < M) ? Trow[sa + 1] : spoolf;
+        T[j].y = (sb < M) ? Trow[sb + 1] : spoolf;
     }
 
     // ---------------- stencil coefficients ---------------------------------------------------
@@ -231,24 +248,27 @@ step_kernel2(const __grid_constant__ SparcParams P, const __grid_constant__ Spar
         cRf = (float)(f * P.k_cond_coeff);
         ncL = -(float)(f * (P.k_cond_coeff + adv));
     }
-    float cE[K], c0[K], cR[K];
+    float2 cE[H], c0[H], cR[H];
     bool convex = false;                        // T' is a convex combination of T, T_diel (no source)
+    auto slot_coeffs = [&](int sl, float hb, float he, float &e_, float &z_, float &r_) {
+        const int i = sl + 1;
+        if (sl < M) {
+            float h = (i >= P.actual_zone_start && i < P.actual_zone_end) ? he : hb;
+            double hA = (double)h * P.A;        // conv_coeff, wire.py:110
+            e_ = (float)(-(f * hA));
+            z_ = (float)(f * hA * P.dielectric_temperature);
+            r_ = (i < N - 1) ? cRf : 0.0f;      // Neumann end, wire.py:95
+        } else {                                // pad slot: pinned near spool_T, feeds nothing
+            e_ = -1.0f;
+            z_ = spoolf;
+            r_ = 0.0f;
+        }
+    };
     auto refresh_coeffs = [&](float hb, float he) {
 #pragma unroll
-        for (int j = 0; j < K; j++) {
-            int sl = lane * K + j;
-            int i = sl + 1;
-            if (sl < M) {
-                float h = (i >= P.actual_zone_start && i < P.actual_zone_end) ? he : hb;
-                double hA = (double)h * P.A;    // conv_coeff, wire.py:110
-                cE[j] = (float)(-(f * hA));
-                c0[j] = (float)(f * hA * P.dielectric_temperature);
-                cR[j] = (i < N - 1) ? cRf : 0.0f;     // Neumann end, wire.py:95
-            } else {                            // pad slot: pinned near spool_T, feeds nothing
-                cE[j] = -1.0f;
-                c0[j] = spoolf;
-                cR[j] = 0.0f;
-            }
+        for (int j = 0; j < H; j++) {
+            slot_coeffs(lane * K + j, hb, he, cE[j].x, c0[j].x, cR[j].x);
+            slot_coeffs(lane * K + j + H, hb, he, cE[j].y, c0[j].y, cR[j].y);
         }
         const float hmax = fmaxf(hb, he), hmin = fminf(hb, he);
         const float ce_max = (float)(f * ((double)hmax * P.A));
@@ -354,9 +374,9 @@ step_kernel2(const __grid_constant__ SparcParams P, const __grid_constant__ Spar
                 bool broke = false;
                 int nx;
                 if (cold_ok && convex)
-                    nx = run_quiet<K, false>(T, cE, c0, cR, ncL, spoolf, lane, n, 0.f, 0.f, crit_count, broke, cold_ok);
+                    nx = run_quiet<H, false>(T, cE, c0, cR, ncL, spoolf, lane, n, 0.f, 0.f, crit_count, broke, cold_ok);
                 else
-                    nx = run_quiet<K, true>(T, cE, c0, cR, ncL, spoolf, lane, n, P.critical_temperature_f32,
+                    nx = run_quiet<H, true>(T, cE, c0, cR, ncL, spoolf, lane, n, P.critical_temperature_f32,
                                             P.breaking_temperature_f32, crit_count, broke, cold_ok);
                 // scalar bookkeeping of the nx quiet µs (ignition.py:302-319, dielectric.py:104-144)
                 int n_idle = nx;
@@ -411,31 +431,35 @@ step_kernel2(const __grid_constant__ SparcParams P, const __grid_constant__ Spar
             // ---- compute_thermal_update with sources (wire.py:58-123) -------------------------
             float lmax = spoolf;
             {
-                float left = __shfl_up_sync(FULL, T[K - 1], 1);
-                const float right = __shfl_down_sync(FULL, T[0], 1);
+                float left = __shfl_up_sync(FULL, T[H - 1].y, 1);
+                const float right = __shfl_down_sync(FULL, T[0].x, 1);
                 if (lane == 0) left = spoolf;
-                float acc[K];
+                float2 acc[H];
 #pragma unroll
-                for (int j = 0; j < K; j++) acc[j] = fmaf(cE[j], T[j], c0[j]);
+                for (int j = 0; j < H; j++) acc[j] = __ffma2_rn(cE[j], T[j], c0[j]);
                 if (s.heat_on) {
                     const float jA = s.jA, jB = s.jB, fP = s.fP;
                     const int jp = (s.spark_state == 1 && s.plasma_idx >= 0 && s.plasma_idx < N)
                                        ? s.plasma_idx - 1 - lane * K : -(1 << 20);
 #pragma unroll
-                    for (int j = 0; j < K; j++) {
-                        if (j >= j_span_lo && j <= j_span_hi) acc[j] += fmaf(jA, T[j], jB);
-                        if (j == jp) acc[j] += fP;
+                    for (int j = 0; j < H; j++) {
+                        if (j >= j_span_lo && j <= j_span_hi) acc[j].x += fmaf(jA, T[j].x, jB);
+                        if (j == jp) acc[j].x += fP;
+                        if (j + H >= j_span_lo && j + H <= j_span_hi) acc[j].y += fmaf(jA, T[j].y, jB);
+                        if (j + H == jp) acc[j].y += fP;
                     }
                 }
-                float dprev = T[0] - left;
+                const float2 ncL2 = make_float2(ncL, ncL);
+                float2 dprev = sub2(T[0], make_float2(left, T[H - 1].x));
+                const float2 last_next = make_float2(T[0].y, right);
 #pragma unroll
-                for (int j = 0; j < K; j++) {
-                    const float dnext = ((j + 1 < K) ? T[j + 1] : right) - T[j];
-                    float q = fmaf(cR[j], dnext, acc[j]);
-                    q = fmaf(ncL, dprev, q);
+                for (int j = 0; j < H; j++) {
+                    const float2 dnext = sub2((j + 1 < H) ? T[j + 1] : last_next, T[j]);
+                    float2 q = __ffma2_rn(cR[j], dnext, acc[j]);
+                    q = __ffma2_rn(ncL2, dprev, q);
                     dprev = dnext;
-                    T[j] = T[j] + q;
-                    lmax = fmaxf(lmax, T[j]);
+                    T[j] = __fadd2_rn(T[j], q);
+                    lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
                 }
             }
             // ---- _check_wire_breaking (wire.py:376-388) ---------------------------------------
@@ -454,9 +478,9 @@ step_kernel2(const __grid_constant__ SparcParams P, const __grid_constant__ Spar
                     if (!(zb > za && zb <= N)) { za = 0; zb = N; }
                     float part = 0.0f;
 #pragma unroll
-                    for (int j = 0; j < K; j++) {
-                        int c = lane * K + j + 1;
-                        if (c >= za && c < zb) part += T[j];
+                    for (int jj = 0; jj < K; jj++) {     // ascending cell order within the lane
+                        int c = lane * K + jj + 1;
+                        if (c >= za && c < zb) part += (jj < H) ? T[jj].x : T[jj - H].y;
                     }
                     if (lane == 0 && za == 0) part += spoolf;    // cell 0 when the zone starts at 0
                     double tot = (double)part;
@@ -491,9 +515,10 @@ step_kernel2(const __grid_constant__ SparcParams P, const __grid_constant__ Spar
 
     // ---------------- store ------------------------------------------------------------------
 #pragma unroll
-    for (int j = 0; j < K; j++) {
-        int sl = lane * K + j;
-        if (sl < M) Trow[sl + 1] = T[j];
+    for (int j = 0; j < H; j++) {
+        const int sa = lane * K + j, sb = sa + H;
+        if (sa < M) Trow[sa + 1] = T[j].x;
+        if (sb < M) Trow[sb + 1] = T[j].y;
     }
     if (lane == 0) {
         const bool thermal_break = (flags & SPARC_F_THERMAL_BREAK) != 0 && tsi_break >= 0;   // broke in THIS call
