@@ -13,7 +13,6 @@
 #include "../../include/sparc_b200.h"
 #include "state_layout.h"
 #include "step_kernel.cuh"
-#include "step_kernel2.cuh"
 
 namespace {
 
@@ -172,45 +171,25 @@ __global__ void fma_peak_kernel(float *out, float a, float b, int iters)
 using StepFn = void (*)(const SparcParams, const SparcStatePtrs, const sparc::StepArgs);
 
 struct Variant {
-    int K, L;
-    StepFn fn[2];    // [INJECT]  per-µs scalar path (step_kernel.cuh)
-    StepFn fn2[2];   // [INJECT]  look-ahead organisation (step_kernel2.cuh), L == 32 only
+    int K;           // cells per lane (even: the stencil is two-wide)
+    StepFn fn[2];    // [INJECT]
 };
 
-#define VARIANT32(K) {K, 32, {sparc::step_kernel<K, 32, false>, sparc::step_kernel<K, 32, true>}, \
-                      {sparc::step_kernel2<K, false>, sparc::step_kernel2<K, true>}}
-#define VARIANT16(K) {K, 16, {sparc::step_kernel<K, 16, false>, sparc::step_kernel<K, 16, true>}, {nullptr, nullptr}}
+#define VARIANT(K) {K, {sparc::step_kernel<K, false>, sparc::step_kernel<K, true>}}
 const Variant kVariants[] = {
-    VARIANT32(4), VARIANT32(8), VARIANT32(12), VARIANT32(14), VARIANT32(16),
-    VARIANT32(20), VARIANT32(24), VARIANT32(28), VARIANT32(36),
-    VARIANT16(24), VARIANT16(26),
+    VARIANT(4), VARIANT(8), VARIANT(12), VARIANT(14), VARIANT(16), VARIANT(20), VARIANT(24), VARIANT(28), VARIANT(36),
 };
-
-// SPARC_KERNEL=1 selects the per-µs kernel (A/B experiments); default is the look-ahead kernel
-bool use_lookahead()
-{
-    const char *s = getenv("SPARC_KERNEL");
-    return !(s && atoi(s) == 1);
-}
 constexpr int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
 
+// smallest variant whose 32 lanes x K slots hold the n_segments-1 dynamic cells
 const Variant *pick_variant(int n_segments)
 {
-    int M = n_segments - 1;
-    int want_L = 32;
-    if (const char *s = getenv("SPARC_LANES_PER_ENV")) want_L = atoi(s);
+    const int M = n_segments - 1;
     const Variant *best = nullptr;
     for (int i = 0; i < kNumVariants; i++) {
         const Variant &v = kVariants[i];
-        if (v.L != want_L || v.K * v.L < M) continue;
+        if (v.K * 32 < M) continue;
         if (!best || v.K < best->K) best = &v;
-    }
-    if (!best && want_L != 32) {
-        for (int i = 0; i < kNumVariants; i++) {
-            const Variant &v = kVariants[i];
-            if (v.L != 32 || v.K * v.L < M) continue;
-            if (!best || v.K < best->K) best = &v;
-        }
     }
     return best;
 }
@@ -243,13 +222,9 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     a.env_id_base = env_id_base;
     a.draws = draws;
     SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
-    int G = 32 / v->L;
-    int warps = (n_envs + G - 1) / G;
-    int wpb = SPARC_BLOCK_THREADS / 32;
-    int blocks = (warps + wpb - 1) / wpb;
-    StepFn fn = v->fn[draws ? 1 : 0];
-    if (v->fn2[0] && use_lookahead()) fn = v->fn2[draws ? 1 : 0];
-    fn<<<blocks, SPARC_BLOCK_THREADS, 0, (cudaStream_t)stream>>>(*p, S, a);
+    const int wpb = SPARC_BLOCK_THREADS / 32;   // one warp per environment
+    const int blocks = (n_envs + wpb - 1) / wpb;
+    v->fn[draws ? 1 : 0]<<<blocks, SPARC_BLOCK_THREADS, 0, (cudaStream_t)stream>>>(*p, S, a);
     CUDA_TRY(cudaGetLastError());
     return SPARC_OK;
 }
@@ -414,13 +389,11 @@ int sparc_launch_info(int n_envs, int n_segments, int32_t out[4])
     if (!out || n_envs <= 0 || n_segments < 2) return fail(SPARC_E_INVALID, "bad launch_info arguments");
     const Variant *v = pick_variant(n_segments);
     if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large for the register-resident kernel");
-    int G = 32 / v->L;
-    int warps = (n_envs + G - 1) / G;
-    int wpb = SPARC_BLOCK_THREADS / 32;
-    out[0] = v->L;
+    const int wpb = SPARC_BLOCK_THREADS / 32;
+    out[0] = 32;
     out[1] = v->K;
     out[2] = SPARC_BLOCK_THREADS;
-    out[3] = (warps + wpb - 1) / wpb;
+    out[3] = (n_envs + wpb - 1) / wpb;
     return SPARC_OK;
 }
 

@@ -1,0 +1,413 @@
+// step_common.cuh — shared pieces of the fused per-µs physics kernel (sm_100a): Philox, the
+// per-env scalar state, and the exact general µs (general_pre).  The kernel is in step_kernel.cuh.
+//
+// One kernel advances every environment through all µs of a step call.  The five reference
+// modules (ignition -> material -> dielectric -> wire -> [break early-return] -> mechanics,
+// src/wedm/envs/wire_edm.py:116-157) are fused; no state touches HBM between µs.
+//
+// Mapping: one warp per environment.  The wire temperature field lives in REGISTERS: each lane
+// owns K consecutive dynamic cells (cell 0 is the spool Dirichlet cell and is a constant).
+// Halos move with two warp shuffles per µs, the wire-break test is a warp vote.  The scalar
+// state machines run in fp64 (bit-compatible with the reference's Python floats; compiled with
+// -fmad=false so no contraction changes their rounding), redundantly on every lane.
+//
+// Stencil arithmetic (reference: Numba kernel, src/wedm/modules/wire.py:58-123): the
+// reference stores T and dT/dt in float32 and evaluates each term in float64.  Here the update
+// is T' = T + dq with dq accumulated in float32 from exact neighbour differences:
+//     dq = cE_j*T_j + c0_j                      convection  (-f*h_j*A*(T_j - T_diel))
+//        + cR_j*(T_{j+1}-T_j) - cL*(T_j-T_{j-1})  conduction + upwind advection
+//        + [I^2>1e-6, contact span] ja*T_j + jb   Joule      (f*J*(1+alpha*(T_j-T_ref)))
+//        + [plasma cell] f*plasma_heat
+// so the only rounding at the magnitude of T is the final add, like the reference's store.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/sparc_b200.h"
+#include "state_layout.h"
+
+namespace sparc {
+
+// ---- Philox4x32-10 (Salmon et al., SC'11); same stream as oracle/wedm_oracle.c ----------
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                              uint32_t k0, uint32_t k1, uint32_t out[4])
+{
+#pragma unroll
+    for (int r = 0; r < 10; r++) {
+        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        uint32_t n0 = hi1 ^ c1 ^ k0;
+        uint32_t n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// uniform in (0,1) from one 32-bit word: (w + 0.5) * 2^-32, exact in fp64
+__device__ __forceinline__ double u01(uint32_t w) { return ((double)w + 0.5) * 2.3283064365386963e-10; }
+
+// CPython float floor-division (Objects/floatobject.c float_divmod), used by the reference for
+// plasma_idx = zone_start + int(y // segment_len)  (wire.py:286-292)
+__device__ __forceinline__ double py_floordiv(double vx, double wx)
+{
+    double mod = fmod(vx, wx);
+    double div = (vx - mod) / wx;
+    if (mod != 0.0) {
+        if ((wx < 0) != (mod < 0)) { mod += wx; div -= 1.0; }
+    }
+    double fd;
+    if (div != 0.0) {
+        fd = floor(div);
+        if (div - fd > 0.5) fd += 1.0;
+    } else {
+        fd = copysign(0.0, vx / wx);
+    }
+    return fd;
+}
+
+// w[idx] without dynamic indexing (keeps the words in registers)
+__device__ __forceinline__ uint32_t pick4(const uint32_t w[4], int idx)
+{
+    uint32_t lo = (idx & 1) ? w[1] : w[0];
+    uint32_t hi = (idx & 1) ? w[3] : w[2];
+    return (idx & 2) ? hi : lo;
+}
+
+}  // namespace sparc
+
+
+namespace sparc {
+
+// Everything the kernel needs besides the state pointers.
+struct StepArgs {
+    SparcActions act;        // device pointers
+    int n_envs, n_us;
+    uint64_t seed;
+    uint32_t env_id_base;
+    const double *draws;     // [n_envs][n_us][5] when INJECT
+};
+
+#ifndef SPARC_BLOCK_THREADS
+#define SPARC_BLOCK_THREADS 128
+#endif
+
+// Sigmoid exponent above which the debris-short probability 1/(1+e^x) < 4.3e-18 can be treated
+// as "cannot fire": on-device uniforms are >= 2^-33; injected draws are checked against U1_SAFE.
+#define SPARC_EXPO_SAFE 40.0
+#define SPARC_U1_SAFE 1.0e-17
+
+// ----------------------------------------------------------------------------------------------
+// Per-env scalar state.  The hot loop keeps the HOT block in registers; everything else lives
+// here (thread-local memory) and is touched only on the rare "general" µs (sparks, shorts,
+// latches, hysteresis refreshes) that run through general_pre().
+// ----------------------------------------------------------------------------------------------
+struct EnvState {
+    // ---- HOT (register-mirrored by the caller) ----
+    double wp, wire, v, prev_accel, target_delta, voltage, debris_volume, win_vsum, gap_prev;
+    int time, spark_state, spark_dur, flags;
+    // ---- cold state ----
+    double debris_density, flow, d_last_gap, d_last_density, w_last_flow;
+    double tv_eff, on_eff, onoff_eff, ipk;
+    int latch_time;          // time at which time_since_servo was 0
+    int tse_ref;             // time at which time_since_spark_end was 0
+    int tsi_prev;            // time_since_spark_ignition before this µs (for the break early-return)
+    int rand_short_rem, deb_short_rem, ion_end, current_mode, win_sparks, win_short_us;
+    bool dens_valid;         // debris_density holds last µs's exact value
+    bool pend_flush;         // last µs's debris flushing has not been applied to debris_volume yet
+    // ---- fast-path constants (valid while fast_ok) ----
+    double gap_lo_f, gap_hi_f, lo_c, hi_c, flush_amt;
+    int onoff_thr;
+    bool fast_ok;
+    // ---- outputs of one general µs for the stencil / caller ----
+    float jA, jB, fP, hb, he;
+    int plasma_idx;
+    bool heat_on, thermal, refresh, freeze, became_done;
+    // ---- context ----
+    int e, it;
+    uint32_t env_id, episode;
+    bool writer;
+    // ---- mechanics state at the start of the current look-ahead block (step_kernel2.cuh) ----
+    double blk_wire, blk_v, blk_pa;
+};
+
+// generator settings as the ignition module sees them (ignition.py:329-343, 98-113): `x or
+// default` (0.0 and None are falsy); peak current of the latched mode.  With fresh-module
+// semantics the reference's caches are pure functions of current_mode: None -> the literal
+// 60.0 A of ignition.py:83; unknown -> default mode.
+__device__ __forceinline__ void derive_generator(EnvState &s, const SparcParams &P, double tv, double on, double off)
+{
+    s.tv_eff = (tv != 0.0) ? tv : P.default_target_voltage;
+    s.on_eff = (on != 0.0) ? on : P.default_on_time;
+    s.onoff_eff = s.on_eff + ((off != 0.0) ? off : P.default_off_time);
+    int mode = s.current_mode;
+    if (mode == 0) s.ipk = 60.0;
+    else s.ipk = P.currents[(mode < 1 || mode > SPARC_MAX_MODE) ? P.default_current_mode : mode];
+    // smallest integer duration d with (double)d >= onoff_eff (rest -> idle, ignition.py:307-309)
+    double c = ceil(s.onoff_eff);
+    s.onoff_thr = (c > 2.0e9) ? 2000000000 : ((c < 0.0) ? 0 : (int)c);
+}
+
+// Exact density of the previous µs and the deferred flushing (dielectric.py:104-144), needed
+// before anything reads debris_density / debris_volume "as the reference has them".
+__device__ __forceinline__ void materialize(EnvState &s, const SparcParams &P)
+{
+    if (!s.dens_valid) {
+        double g = (s.gap_prev > 0.001) ? s.gap_prev : 0.001;
+        double cavity = P.cavity_volume_coeff * (g * 0.001);
+        if (cavity > 0.0) {
+            double d = s.debris_volume / cavity;
+            s.debris_density = (d < 1.0) ? d : 1.0;
+        } else s.debris_density = 0.0;
+        s.dens_valid = true;
+    }
+    if (s.pend_flush) {
+        if (s.flow > 0.001 && s.debris_volume > 0.001) {
+            double nv = s.debris_volume - P.debris_removal_per_us * s.flow;
+            s.debris_volume = (nv > 0.0) ? nv : 0.0;
+        }
+        s.pend_flush = false;
+    }
+}
+
+// Decide whether the quiet-µs fast path may run next and precompute its constants.  Every bound
+// is shrunk by an absolute 1e-9 so that the reference's own floating-point comparisons
+// (|gap-last| > 0.01, |rho-last| > 0.001, sigmoid exponent) provably resolve the same way.
+__device__ __forceinline__ void prepare_fast(EnvState &s, const SparcParams &P)
+{
+    const double M = 1e-9;
+    bool ok = (s.rand_short_rem | s.deb_short_rem) == 0 && (s.flags & SPARC_F_DONE) == 0;
+    double lo = s.d_last_gap - 0.01 + M, hi = s.d_last_gap + 0.01 - M;
+    double need = (P.hard_short_gap > 0.001) ? P.hard_short_gap : 0.001;
+    if (P.random_short_max_probability > 0.0 && P.random_short_max_gap > need) need = P.random_short_max_gap;
+    need += M;
+    if (lo < need) lo = need;
+    ok = ok && (lo <= hi) && (hi < 1.0e6);
+    // debris-short sigmoid must stay negligible for every gap in [lo,hi] and every density in the band
+    double crit = P.base_critical_density + P.gap_coefficient * ((P.gap_coefficient >= 0.0) ? lo : hi);
+    crit = (P.max_critical_density < crit) ? P.max_critical_density : crit;
+    double dens_hi = s.d_last_density + 0.001;
+    ok = ok && (P.sigmoid_steepness > 0.0) && (dens_hi < crit - SPARC_EXPO_SAFE / P.sigmoid_steepness - M);
+    ok = ok && (s.debris_density <= dens_hi);
+    // density band  |rho - last| <= 0.001  <=>  lo_c*gap <= debris <= hi_c*gap   (rho < 1)
+    double k = P.cavity_volume_coeff * 0.001;
+    ok = ok && (k > 0.0) && (dens_hi < 1.0);
+    s.lo_c = (s.d_last_density - 0.001 + M) * k;
+    s.hi_c = (dens_hi - M) * k;
+    // deferred flushing: debris - amt must stay positive whenever debris > 0.001
+    s.flush_amt = (s.flow > 0.001) ? P.debris_removal_per_us * s.flow : 0.0;
+    ok = ok && (s.flush_amt >= 0.0) && (s.flush_amt < 0.001);
+    s.gap_lo_f = lo;
+    s.gap_hi_f = hi;
+    s.fast_ok = ok;
+}
+
+// ----------------------------------------------------------------------------------------------
+// The general µs: everything before the thermal stencil, exactly in the reference's order
+// (wire_edm.py:117-127).  Rare (sparks, shorts, latches, hysteresis refreshes, first µs of a
+// call), so it is kept out of line and works on the EnvState in local memory.
+// ----------------------------------------------------------------------------------------------
+template <bool INJECT>
+__device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, const SparcStatePtrs &S,
+                                         const StepArgs &a)
+{
+    const int e = s.e;
+    const uint32_t k0 = (uint32_t)a.seed, k1 = (uint32_t)(a.seed >> 32);
+    auto draw = [&](int slot) -> double {
+        if (INJECT) return a.draws[((size_t)e * a.n_us + s.it) * SPARC_N_DRAW_SLOTS + slot];
+        uint32_t w[4];
+        philox4x32_10(s.env_id, (uint32_t)s.time >> 2, s.episode, (uint32_t)slot, k0, k1, w);
+        return u01(pick4(w, s.time & 3));
+    };
+    s.heat_on = false; s.refresh = false; s.freeze = false; s.became_done = false;
+    s.jA = 0.0f; s.jB = 0.0f; s.fP = 0.0f;
+    s.thermal = true;
+    s.tsi_prev = (s.spark_state == 1) ? s.spark_dur + 1 : 0;
+    materialize(s, P);
+
+    // ---- step(): action latch (wire_edm.py:117-121, 162-170) ---------------------------------
+    if (s.time - s.latch_time >= P.servo_interval) {
+        const double a_tv = (double)a.act.target_voltage[e];
+        const double a_on = (double)a.act.on_time[e];
+        const double a_off = (double)a.act.off_time[e];
+        const int a_mode = a.act.current_mode[e];
+        s.target_delta = (double)a.act.servo[e];
+        s.current_mode = (a_mode == 0) ? -1 : a_mode;       // "I0" is a string, not None
+        derive_generator(s, P, a_tv, a_on, a_off);
+        if (s.writer) { S.target_voltage[e] = a_tv; S.on_time[e] = a_on; S.off_time[e] = a_off; }
+        s.latch_time = s.time;
+    }
+
+    // ---- IgnitionModule._update_short_circuit_detection (ignition.py:197-245) ----------------
+    const double gap_raw = s.wp - s.wire;
+    const double gap = (gap_raw > 0.0) ? gap_raw : 0.0;
+    bool is_short;
+    if (s.rand_short_rem > 0) { s.rand_short_rem -= 1; is_short = true; }
+    else if (s.deb_short_rem > 0) { s.deb_short_rem -= 1; is_short = true; }
+    else {
+        is_short = false;
+        double p_deb;                                       // ignition.py:115-146
+        bool tiny = false;                                  // 0 < p_deb < 4.3e-18
+        if (gap < P.hard_short_gap) p_deb = 1.0;
+        else {
+            double crit = P.base_critical_density + P.gap_coefficient * gap;
+            crit = (P.max_critical_density < crit) ? P.max_critical_density : crit;
+            double expo = -P.sigmoid_steepness * (s.debris_density - crit);
+            if (expo > 500.0) p_deb = 0.0;
+            else if (expo < -500.0) p_deb = 1.0;
+            else if (!INJECT && expo > SPARC_EXPO_SAFE) { p_deb = 0.0; tiny = true; }
+            else p_deb = 1.0 / (1.0 + exp(expo));
+        }
+        (void)tiny;
+        double p_rnd;
+        if (gap >= P.random_short_max_gap) p_rnd = 0.0;
+        else if (gap <= P.random_short_min_gap) p_rnd = P.random_short_max_probability;
+        else {
+            double gf = 1.0 - (gap - P.random_short_min_gap) / (P.random_short_max_gap - P.random_short_min_gap);
+            p_rnd = gf * P.random_short_max_probability;
+        }
+        if (p_deb > 0.0 && draw(0) < p_deb) {
+            s.deb_short_rem = P.debris_short_duration;
+            is_short = true;
+            if (s.writer) S.stat_short_events[e] += 1;
+        } else if (p_rnd > 0.0 && draw(1) < p_rnd) {
+            s.rand_short_rem = P.random_short_duration;
+            is_short = true;
+            if (s.writer) S.stat_short_events[e] += 1;
+        }
+    }
+    if (is_short) s.voltage = 0.0;
+
+    // ---- state machine (ignition.py:186-195, 247-319) ----------------------------------------
+    bool fresh_spark = false;
+    if (s.spark_state == 0) {
+        if (is_short) {
+            s.spark_state = -1; s.flags &= ~SPARC_F_HAS_Y; s.spark_dur = 0;
+            if (s.writer) { S.stat_pulse_short[e] += 1; S.spark_y[e] = -1.0; }
+        } else {
+            s.voltage = s.tv_eff;
+            const double u3 = draw(2);
+            // get_lambda (ignition.py:348-364): ln2 / (a*gap^2 + b*gap + c), raw gap
+            double den = P.ignition_a_coeff * (gap_raw * gap_raw) + P.ignition_b_coeff * gap_raw + P.ignition_c_coeff;
+            if (u3 < 0.6931471805599453 / den) {
+                double y = 0.0 + (P.workpiece_height - 0.0) * draw(3);      // Generator.uniform
+                s.spark_state = 1; s.flags |= SPARC_F_HAS_Y; s.spark_dur = 0;
+                s.voltage = s.tv_eff * P.spark_voltage_factor;
+                s.win_sparks += 1;
+                fresh_spark = true;
+                s.plasma_idx = (P.segment_len != 0.0) ? P.zone_start + (int)py_floordiv(y, P.segment_len) : P.zone_start;
+                if (s.writer) { S.stat_sparks[e] += 1; S.spark_y[e] = y; }
+            }
+        }
+    } else if (s.spark_state == 1) {
+        s.spark_dur += 1;
+        if ((double)s.spark_dur >= s.on_eff) { s.spark_state = -2; if (!is_short) s.voltage = 0.0; }
+        else if (!is_short) s.voltage = s.tv_eff * P.spark_voltage_factor;
+    } else if (s.spark_state == -1) {
+        s.spark_dur += 1;
+        if ((double)s.spark_dur >= s.on_eff) s.spark_state = -2;
+    } else {  // -2 rest
+        s.spark_dur += 1;
+        if ((double)s.spark_dur >= s.onoff_eff) {
+            s.spark_state = 0; s.flags &= ~SPARC_F_HAS_Y; s.spark_dur = 0;
+            if (s.writer) S.spark_y[e] = -1.0;
+            if (!is_short) s.voltage = s.tv_eff;
+        } else if (!is_short) s.voltage = 0.0;
+    }
+    if (is_short) { s.flags |= SPARC_F_SHORT; s.win_short_us += 1; }
+    else s.flags &= ~SPARC_F_SHORT;
+    s.win_vsum += s.voltage;
+    // state.current is reassigned on every path above: Ipk in spark / short-pulse, else 0
+    const double current = (s.spark_state == 1 || s.spark_state == -1) ? s.ipk : 0.0;
+
+    // ---- MaterialRemovalModule.update (material.py:79-174) -----------------------------------
+    double crater_volume = 0.0;                             // state.last_crater_volume [mm^3]
+    if (fresh_spark) {
+        const int mode = (s.current_mode == 0) ? 1 : s.current_mode;       // material.py:104-105
+        if (mode < 1 || mode > SPARC_MAX_MODE || !P.crater_avail[mode]) {
+            s.flags |= SPARC_F_MODE_ERROR;                  // the reference raises ValueError here
+            s.became_done = true; s.thermal = false; s.freeze = true;
+            s.fast_ok = false;
+            return;
+        }
+        double z;
+        if (INJECT) z = draw(4);
+        else {
+            uint32_t w[4];
+            philox4x32_10(s.env_id, (uint32_t)s.time, s.episode, 4u, k0, k1, w);
+            z = sqrt(-2.0 * log(u01(w[0]))) * cospi(2.0 * u01(w[1]));
+        }
+        double vol_um3 = P.crater_mean[mode] + P.crater_std[mode] * z;
+        vol_um3 = (vol_um3 > 0.0) ? vol_um3 : 0.0;
+        crater_volume = vol_um3 / 1e9;
+        if (crater_volume > 0.0) {
+            double kh = P.kerf_times_height[mode];
+            double dx_um = 0.0;
+            if (kh > 0.0) dx_um = (crater_volume / kh) * 1000.0;
+            s.wp += dx_um;
+        }
+        if (s.writer) {
+            S.stat_crater_sum[e] += vol_um3;
+            S.last_crater_volume[e] = crater_volume;
+            if (s.current_mode != 0) S.mat_cached_mode[e] = mode;
+            S.mat_info_mode[e] = mode;
+        }
+    }
+
+    // ---- DielectricModule.update (dielectric.py:82-163) --------------------------------------
+    double gap_um = s.wp - s.wire;
+    gap_um = (gap_um > 0.001) ? gap_um : 0.001;
+    s.gap_prev = gap_um;
+    const double cavity_volume = P.cavity_volume_coeff * (gap_um * 0.001);
+    if (crater_volume > 0.0) {                              // fresh spark with a crater
+        s.debris_volume += crater_volume;
+        s.ion_end = s.time + P.ion_channel_duration;        // ion_rem = max(0, ion_end - time)
+    }
+    if (cavity_volume > 0.0) {
+        double d = s.debris_volume / cavity_volume;
+        s.debris_density = (d < 1.0) ? d : 1.0;
+    } else s.debris_density = 0.0;
+    s.dens_valid = true;
+    if (fabs(gap_um - s.d_last_gap) > 0.01 || fabs(s.debris_density - s.d_last_density) > 0.001) {
+        double r = gap_um / P.reference_gap;
+        double gf = r * r * r;                              // (gap/ref)**3
+        gf = (gf < 1.0) ? gf : 1.0;
+        double x = P.debris_obstruction_coeff * s.debris_density;
+        double df;
+        if (x < 0.5) df = (1.0 - 0.5 * x) / (1.0 + 0.5 * x);               // fast_exp Pade branch
+        else df = exp(-x);
+        s.flow = gf * df;
+        s.d_last_gap = gap_um;
+        s.d_last_density = s.debris_density;
+    }
+    s.pend_flush = true;                                    // flushing of this µs applied lazily
+
+    // ---- WireModule.update, host part (wire.py:259-309, 349-374) -----------------------------
+    if (fabs(s.flow - s.w_last_flow) > 0.01) {
+        double ve = P.convection_velocity_factor * S.unwind_v[e];
+        ve = (ve > -0.9) ? ve : -0.9;
+        double hb = P.base_convection_coefficient * (1.0 + ve);
+        double hfloor = 0.1 * P.base_convection_coefficient;
+        hb = (hb > hfloor) ? hb : hfloor;
+        double he = hb * (1.0 + P.convection_flow_enhancement * s.flow);
+        s.hb = (float)hb; s.he = (float)he; s.refresh = true;
+        if (s.writer) { S.h_base[e] = s.hb; S.h_enh[e] = s.he; }
+        s.w_last_flow = s.flow;
+    }
+    if (current * current > 1e-6) {                         // wire.py:98-102
+        const double f = P.temp_update_factor;
+        double jf = f * (P.joule_geom_factor * (current * current) * P.rho_elec);
+        s.jA = (float)(jf * P.alpha_rho);
+        s.jB = (float)(jf * (1.0 - P.alpha_rho * P.temp_ref));
+        s.heat_on = true;
+        if (s.spark_state == 1) {                           // plasma spot, wire.py:293-297
+            double ph = P.plasma_efficiency * s.voltage * current;
+            if (!isfinite(ph)) ph = 0.0;
+            s.fP = (float)(f * ph);
+        }
+    }
+    prepare_fast(s, P);
+}
+
+}  // namespace sparc

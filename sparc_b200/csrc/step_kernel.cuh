@@ -1,449 +1,179 @@
-// step_kernel.cuh — the fused per-µs physics kernel (sm_100a).
+// step_kernel.cuh — the fused step kernel, "look-ahead" organisation (sm_100a).
 //
-// One kernel advances every environment through all µs of a step call.  The five reference
-// modules (ignition -> material -> dielectric -> wire -> [break early-return] -> mechanics,
-// src/wedm/envs/wire_edm.py:116-157) are fused; no state touches HBM between µs.
+// Same mapping as step_kernel.cuh (one warp per environment, the wire temperature field in
+// registers, K cells per lane, halos by warp shuffle) and the same general µs (general_pre), but
+// the per-µs scalar state machines no longer run on every µs:
 //
-// Mapping: L lanes (32, 16 or 8) cooperate on one environment; 32/L environments share a warp.
-// The wire temperature field lives in REGISTERS: lane `sub` owns K consecutive dynamic cells
-// (cell 0 is the spool Dirichlet cell and is a constant).  Halos move with two warp shuffles
-// per µs, the wire-break test is a warp vote.  The O(1)-per-µs scalar state machines run
-// redundantly on every lane of the group in fp64 (bit-compatible with the reference's Python
-// floats; compiled with -fmad=false so no contraction changes their rounding).
+//   * MECHANICS (mechanics.py:79-114) depends on nothing but the latched servo command, so it is
+//     advanced one BLOCK of <= 32 µs ahead of everything else (exact sequential fp64, identical
+//     operations); the 32 wire positions go to shared memory and from there one per lane.
+//   * LOOK-AHEAD: lane l then evaluates, for µs l of the block, every condition under which the
+//     reference's step() is "quiet" (idle/rest, no latch, no short circuit, no ignition, no
+//     hysteresis refresh, no collision, no zone-mean sample).  The ignition roll is evaluated
+//     here too: lane l computes the Philox word of its own µs.  One ballot gives the length n of
+//     the quiet run.
+//   * QUIET RUN: n µs of pure stencil — no scalar instruction in the loop.  When the wire is
+//     provably cold (max T < critical-1 K and the update is a convex combination, so the maximum
+//     cannot grow without a heat source) even the max/break test is skipped.
+//   * everything else takes the exact general µs (general_pre + heated stencil + break test +
+//     termination), one µs at a time.
 //
-// Stencil arithmetic (reference: Numba kernel, src/wedm/modules/wire.py:58-123): the
-// reference stores T and dT/dt in float32 and evaluates each term in float64.  Here the update
-// is T' = T + dq with dq accumulated in float32 from exact neighbour differences:
-//     dq = cE_j*T_j + c0_j                      convection  (-f*h_j*A*(T_j - T_diel))
-//        + cR_j*(T_{j+1}-T_j) - cL*(T_j-T_{j-1})  conduction + upwind advection
-//        + [I^2>1e-6, contact span] ja*T_j + jb   Joule      (f*J*(1+alpha*(T_j-T_ref)))
-//        + [plasma cell] f*plasma_heat
-// so the only rounding at the magnitude of T is the final add, like the reference's store.
+// Every shortcut is conservative: a µs that is not provably quiet runs the general path, which is
+// the reference's logic statement by statement, so results do not depend on where the run boundaries fall.
 #pragma once
-#include <cuda_runtime.h>
-#include <stdint.h>
-
-#include "../../include/sparc_b200.h"
-#include "state_layout.h"
+#include "step_common.cuh"
 
 namespace sparc {
 
-// ---- Philox4x32-10 (Salmon et al., SC'11); same stream as oracle/wedm_oracle.c ----------
-__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                                              uint32_t k0, uint32_t k1, uint32_t out[4])
+// MechanicsModule.update (mechanics.py:79-114), one µs.
+__device__ __forceinline__ void mech_step(const SparcParams &P, double &wire, double &v, double &prev_accel,
+                                          const double target_delta)
 {
-#pragma unroll
-    for (int r = 0; r < 10; r++) {
-        uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
-        uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
-        uint32_t n0 = hi1 ^ c1 ^ k0;
-        uint32_t n2 = hi0 ^ c3 ^ k1;
-        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
-        k0 += 0x9E3779B9u;
-        k1 += 0xBB67AE85u;
-    }
-    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
-}
-
-// uniform in (0,1) from one 32-bit word: (w + 0.5) * 2^-32, exact in fp64
-__device__ __forceinline__ double u01(uint32_t w) { return ((double)w + 0.5) * 2.3283064365386963e-10; }
-
-// CPython float floor-division (Objects/floatobject.c float_divmod), used by the reference for
-// plasma_idx = zone_start + int(y // segment_len)  (wire.py:286-292)
-__device__ __forceinline__ double py_floordiv(double vx, double wx)
-{
-    double mod = fmod(vx, wx);
-    double div = (vx - mod) / wx;
-    if (mod != 0.0) {
-        if ((wx < 0) != (mod < 0)) { mod += wx; div -= 1.0; }
-    }
-    double fd;
-    if (div != 0.0) {
-        fd = floor(div);
-        if (div - fd > 0.5) fd += 1.0;
+    double a_nom;
+    if (P.control_mode == 0) {
+        double x_err = wire - (wire + target_delta);
+        a_nom = P.damping_coeff * v + P.stiffness_coeff * x_err;
     } else {
-        fd = copysign(0.0, vx / wx);
+        a_nom = -P.omega_n * (v - target_delta);
     }
-    return fd;
+    double da = a_nom - prev_accel;
+    if (fabs(a_nom) <= P.max_acceleration && fabs(da) <= P.max_jerk_dt) {
+        prev_accel = prev_accel + da;           // no clip active
+    } else {
+        if (a_nom > P.max_acceleration) a_nom = P.max_acceleration;
+        else if (a_nom < -P.max_acceleration) a_nom = -P.max_acceleration;
+        da = a_nom - prev_accel;
+        if (da > P.max_jerk_dt) da = P.max_jerk_dt;
+        else if (da < -P.max_jerk_dt) da = -P.max_jerk_dt;
+        prev_accel = prev_accel + da;
+    }
+    v += prev_accel * P.mech_dt;
+    if (!(fabs(v) <= P.max_speed)) {
+        if (v > P.max_speed) v = P.max_speed;
+        else if (v < -P.max_speed) v = -P.max_speed;
+    }
+    wire += v * P.mech_dt;
 }
 
-template <int L>
-__device__ __forceinline__ unsigned group_mask(int grp)
+// nb µs of mechanics assuming no acceleration / jerk / speed clip is active (then the update is
+// the same operation sequence as mech_step without its branches).  Returns false if any clip
+// condition was met on any µs: the caller redoes the block with mech_step.
+__device__ __forceinline__ bool mech_block_noclip(const SparcParams &P, double &wire, double &v, double &prev_accel,
+                                                  const double target_delta, const int nb, double *post_s,
+                                                  const bool writer)
 {
-    if constexpr (L == 32) return 0xffffffffu;
-    else return ((1u << L) - 1u) << (grp * L);
+    const double dt = P.mech_dt;
+    bool bad = false;
+    if (P.control_mode == 0) {
+        const double c1 = P.damping_coeff, c2 = P.stiffness_coeff;
+#pragma unroll 4
+        for (int k = 0; k < nb; k++) {
+            const double x_err = wire - (wire + target_delta);
+            const double a_nom = c1 * v + c2 * x_err;
+            const double da = a_nom - prev_accel;
+            bad = bad || !(fabs(a_nom) <= P.max_acceleration) || !(fabs(da) <= P.max_jerk_dt);
+            prev_accel = prev_accel + da;
+            v += prev_accel * dt;
+            bad = bad || !(fabs(v) <= P.max_speed);
+            wire += v * dt;
+            if (writer) post_s[k] = wire;
+        }
+    } else {
+        const double nw = -P.omega_n;
+#pragma unroll 4
+        for (int k = 0; k < nb; k++) {
+            const double a_nom = nw * (v - target_delta);
+            const double da = a_nom - prev_accel;
+            bad = bad || !(fabs(a_nom) <= P.max_acceleration) || !(fabs(da) <= P.max_jerk_dt);
+            prev_accel = prev_accel + da;
+            v += prev_accel * dt;
+            bad = bad || !(fabs(v) <= P.max_speed);
+            wire += v * dt;
+            if (writer) post_s[k] = wire;
+        }
+    }
+    return !bad;
 }
 
-// w[idx] without dynamic indexing (keeps the words in registers)
-__device__ __forceinline__ uint32_t pick4(const uint32_t w[4], int idx)
+// ---- packed stencil ---------------------------------------------------------------------------
+// sm_100 has two-wide fp32 instructions (FFMA2/FADD2, PTX fma.rn.f32x2): one issue slot and one
+// pipe pass for two IEEE-rn operations — measured 1.95 FFMA2 vs 2.1 register-operand FFMA per
+// clock per SM (tools/microbench2.cu).  Lane cells are split in two halves of H = K/2 cells;
+// pair j holds (T[j], T[j+H]) so that neighbour differences of pair j are pair j+1 minus pair j.
+// Element-wise the operation sequence is unchanged: q = fma(cE,T,c0); q = fma(cR,dnext,q);
+// q = fma(ncL,dprev,q); T = T + q.
+__device__ __forceinline__ float2 sub2(const float2 a, const float2 b)
 {
-    uint32_t lo = (idx & 1) ? w[1] : w[0];
-    uint32_t hi = (idx & 1) ? w[3] : w[2];
-    return (idx & 2) ? hi : lo;
+    return __fadd2_rn(a, make_float2(-b.x, -b.y));
 }
 
-}  // namespace sparc
-
-
-namespace sparc {
-
-// Everything the kernel needs besides the state pointers.
-struct StepArgs {
-    SparcActions act;        // device pointers
-    int n_envs, n_us;
-    uint64_t seed;
-    uint32_t env_id_base;
-    const double *draws;     // [n_envs][n_us][5] when INJECT
-};
-
-#define SPARC_BLOCK_THREADS 128
-
-// Sigmoid exponent above which the debris-short probability 1/(1+e^x) < 4.3e-18 can be treated
-// as "cannot fire": on-device uniforms are >= 2^-33; injected draws are checked against U1_SAFE.
-#define SPARC_EXPO_SAFE 40.0
-#define SPARC_U1_SAFE 1.0e-17
-
-// ----------------------------------------------------------------------------------------------
-// Per-env scalar state.  The hot loop keeps the HOT block in registers; everything else lives
-// here (thread-local memory) and is touched only on the rare "general" µs (sparks, shorts,
-// latches, hysteresis refreshes) that run through general_pre().
-// ----------------------------------------------------------------------------------------------
-struct EnvState {
-    // ---- HOT (register-mirrored by the caller) ----
-    double wp, wire, v, prev_accel, target_delta, voltage, debris_volume, win_vsum, gap_prev;
-    int time, spark_state, spark_dur, flags;
-    // ---- cold state ----
-    double debris_density, flow, d_last_gap, d_last_density, w_last_flow;
-    double tv_eff, on_eff, onoff_eff, ipk;
-    int latch_time;          // time at which time_since_servo was 0
-    int tse_ref;             // time at which time_since_spark_end was 0
-    int tsi_prev;            // time_since_spark_ignition before this µs (for the break early-return)
-    int rand_short_rem, deb_short_rem, ion_end, current_mode, win_sparks, win_short_us;
-    bool dens_valid;         // debris_density holds last µs's exact value
-    bool pend_flush;         // last µs's debris flushing has not been applied to debris_volume yet
-    // ---- fast-path constants (valid while fast_ok) ----
-    double gap_lo_f, gap_hi_f, lo_c, hi_c, flush_amt;
-    int onoff_thr;
-    bool fast_ok;
-    // ---- outputs of one general µs for the stencil / caller ----
-    float jA, jB, fP, hb, he;
-    int plasma_idx;
-    bool heat_on, thermal, refresh, freeze, became_done;
-    // ---- context ----
-    int e, it;
-    uint32_t env_id, episode;
-    bool writer;
-    // ---- mechanics state at the start of the current look-ahead block (step_kernel2.cuh) ----
-    double blk_wire, blk_v, blk_pa;
-};
-
-// generator settings as the ignition module sees them (ignition.py:329-343, 98-113): `x or
-// default` (0.0 and None are falsy); peak current of the latched mode.  With fresh-module
-// semantics the reference's caches are pure functions of current_mode: None -> the literal
-// 60.0 A of ignition.py:83; unknown -> default mode.
-__device__ __forceinline__ void derive_generator(EnvState &s, const SparcParams &P, double tv, double on, double off)
+// n quiet µs of compute_thermal_update (wire.py:58-123) without heat sources.  HOT additionally
+// runs _check_wire_breaking (wire.py:376-388) every µs and returns the number of µs executed
+// (n, or j+1 when the wire broke on µs j; `broke` says which).
+template <int H, bool HOT>
+__device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], const float2 (&c0)[H],
+                                         const float2 (&cR)[H], const float ncL, const float spoolf, const int lane,
+                                         const int n, const float crit_T, const float break_T, int &crit_count,
+                                         bool &broke, bool &cold_after)
 {
-    s.tv_eff = (tv != 0.0) ? tv : P.default_target_voltage;
-    s.on_eff = (on != 0.0) ? on : P.default_on_time;
-    s.onoff_eff = s.on_eff + ((off != 0.0) ? off : P.default_off_time);
-    int mode = s.current_mode;
-    if (mode == 0) s.ipk = 60.0;
-    else s.ipk = P.currents[(mode < 1 || mode > SPARC_MAX_MODE) ? P.default_current_mode : mode];
-    // smallest integer duration d with (double)d >= onoff_eff (rest -> idle, ignition.py:307-309)
-    double c = ceil(s.onoff_eff);
-    s.onoff_thr = (c > 2.0e9) ? 2000000000 : ((c < 0.0) ? 0 : (int)c);
+    constexpr unsigned FULL = 0xffffffffu;
+    const float2 ncL2 = make_float2(ncL, ncL);
+    broke = false;
+#pragma unroll 1
+    for (int k = 0; k < n; k++) {
+        float left = __shfl_up_sync(FULL, T[H - 1].y, 1);
+        const float right = __shfl_down_sync(FULL, T[0].x, 1);
+        if (lane == 0) left = spoolf;
+        float2 dprev = sub2(T[0], make_float2(left, T[H - 1].x));
+        const float2 last_next = make_float2(T[0].y, right);
+        float lmax = spoolf;
+#pragma unroll
+        for (int j = 0; j < H; j++) {
+            const float2 dnext = sub2((j + 1 < H) ? T[j + 1] : last_next, T[j]);
+            float2 q = __ffma2_rn(cE[j], T[j], c0[j]);
+            q = __ffma2_rn(cR[j], dnext, q);
+            q = __ffma2_rn(ncL2, dprev, q);
+            dprev = dnext;
+            T[j] = __fadd2_rn(T[j], q);
+            if (HOT) lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
+        }
+        if (HOT) {
+            const bool hot = __any_sync(FULL, lmax > crit_T);
+            crit_count = hot ? crit_count + 1 : 0;
+            if (hot && __any_sync(FULL, lmax > break_T)) { broke = true; return k + 1; }
+            if (k == n - 1) cold_after = !__any_sync(FULL, lmax > crit_T - 1.0f);
+        }
+    }
+    if (!HOT) crit_count = 0;
+    return n;
 }
 
-// Exact density of the previous µs and the deferred flushing (dielectric.py:104-144), needed
-// before anything reads debris_density / debris_volume "as the reference has them".
-__device__ __forceinline__ void materialize(EnvState &s, const SparcParams &P)
-{
-    if (!s.dens_valid) {
-        double g = (s.gap_prev > 0.001) ? s.gap_prev : 0.001;
-        double cavity = P.cavity_volume_coeff * (g * 0.001);
-        if (cavity > 0.0) {
-            double d = s.debris_volume / cavity;
-            s.debris_density = (d < 1.0) ? d : 1.0;
-        } else s.debris_density = 0.0;
-        s.dens_valid = true;
-    }
-    if (s.pend_flush) {
-        if (s.flow > 0.001 && s.debris_volume > 0.001) {
-            double nv = s.debris_volume - P.debris_removal_per_us * s.flow;
-            s.debris_volume = (nv > 0.0) ? nv : 0.0;
-        }
-        s.pend_flush = false;
-    }
-}
-
-// Decide whether the quiet-µs fast path may run next and precompute its constants.  Every bound
-// is shrunk by an absolute 1e-9 so that the reference's own floating-point comparisons
-// (|gap-last| > 0.01, |rho-last| > 0.001, sigmoid exponent) provably resolve the same way.
-__device__ __forceinline__ void prepare_fast(EnvState &s, const SparcParams &P)
-{
-    const double M = 1e-9;
-    bool ok = (s.rand_short_rem | s.deb_short_rem) == 0 && (s.flags & SPARC_F_DONE) == 0;
-    double lo = s.d_last_gap - 0.01 + M, hi = s.d_last_gap + 0.01 - M;
-    double need = (P.hard_short_gap > 0.001) ? P.hard_short_gap : 0.001;
-    if (P.random_short_max_probability > 0.0 && P.random_short_max_gap > need) need = P.random_short_max_gap;
-    need += M;
-    if (lo < need) lo = need;
-    ok = ok && (lo <= hi) && (hi < 1.0e6);
-    // debris-short sigmoid must stay negligible for every gap in [lo,hi] and every density in the band
-    double crit = P.base_critical_density + P.gap_coefficient * ((P.gap_coefficient >= 0.0) ? lo : hi);
-    crit = (P.max_critical_density < crit) ? P.max_critical_density : crit;
-    double dens_hi = s.d_last_density + 0.001;
-    ok = ok && (P.sigmoid_steepness > 0.0) && (dens_hi < crit - SPARC_EXPO_SAFE / P.sigmoid_steepness - M);
-    ok = ok && (s.debris_density <= dens_hi);
-    // density band  |rho - last| <= 0.001  <=>  lo_c*gap <= debris <= hi_c*gap   (rho < 1)
-    double k = P.cavity_volume_coeff * 0.001;
-    ok = ok && (k > 0.0) && (dens_hi < 1.0);
-    s.lo_c = (s.d_last_density - 0.001 + M) * k;
-    s.hi_c = (dens_hi - M) * k;
-    // deferred flushing: debris - amt must stay positive whenever debris > 0.001
-    s.flush_amt = (s.flow > 0.001) ? P.debris_removal_per_us * s.flow : 0.0;
-    ok = ok && (s.flush_amt >= 0.0) && (s.flush_amt < 0.001);
-    s.gap_lo_f = lo;
-    s.gap_hi_f = hi;
-    s.fast_ok = ok;
-}
-
-// ----------------------------------------------------------------------------------------------
-// The general µs: everything before the thermal stencil, exactly in the reference's order
-// (wire_edm.py:117-127).  Rare (sparks, shorts, latches, hysteresis refreshes, first µs of a
-// call), so it is kept out of line and works on the EnvState in local memory.
-// ----------------------------------------------------------------------------------------------
-template <bool INJECT>
-__device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, const SparcStatePtrs &S,
-                                         const StepArgs &a)
-{
-    const int e = s.e;
-    const uint32_t k0 = (uint32_t)a.seed, k1 = (uint32_t)(a.seed >> 32);
-    auto draw = [&](int slot) -> double {
-        if (INJECT) return a.draws[((size_t)e * a.n_us + s.it) * SPARC_N_DRAW_SLOTS + slot];
-        uint32_t w[4];
-        philox4x32_10(s.env_id, (uint32_t)s.time >> 2, s.episode, (uint32_t)slot, k0, k1, w);
-        return u01(pick4(w, s.time & 3));
-    };
-    s.heat_on = false; s.refresh = false; s.freeze = false; s.became_done = false;
-    s.jA = 0.0f; s.jB = 0.0f; s.fP = 0.0f;
-    s.thermal = true;
-    s.tsi_prev = (s.spark_state == 1) ? s.spark_dur + 1 : 0;
-    materialize(s, P);
-
-    // ---- step(): action latch (wire_edm.py:117-121, 162-170) ---------------------------------
-    if (s.time - s.latch_time >= P.servo_interval) {
-        const double a_tv = (double)a.act.target_voltage[e];
-        const double a_on = (double)a.act.on_time[e];
-        const double a_off = (double)a.act.off_time[e];
-        const int a_mode = a.act.current_mode[e];
-        s.target_delta = (double)a.act.servo[e];
-        s.current_mode = (a_mode == 0) ? -1 : a_mode;       // "I0" is a string, not None
-        derive_generator(s, P, a_tv, a_on, a_off);
-        if (s.writer) { S.target_voltage[e] = a_tv; S.on_time[e] = a_on; S.off_time[e] = a_off; }
-        s.latch_time = s.time;
-    }
-
-    // ---- IgnitionModule._update_short_circuit_detection (ignition.py:197-245) ----------------
-    const double gap_raw = s.wp - s.wire;
-    const double gap = (gap_raw > 0.0) ? gap_raw : 0.0;
-    bool is_short;
-    if (s.rand_short_rem > 0) { s.rand_short_rem -= 1; is_short = true; }
-    else if (s.deb_short_rem > 0) { s.deb_short_rem -= 1; is_short = true; }
-    else {
-        is_short = false;
-        double p_deb;                                       // ignition.py:115-146
-        bool tiny = false;                                  // 0 < p_deb < 4.3e-18
-        if (gap < P.hard_short_gap) p_deb = 1.0;
-        else {
-            double crit = P.base_critical_density + P.gap_coefficient * gap;
-            crit = (P.max_critical_density < crit) ? P.max_critical_density : crit;
-            double expo = -P.sigmoid_steepness * (s.debris_density - crit);
-            if (expo > 500.0) p_deb = 0.0;
-            else if (expo < -500.0) p_deb = 1.0;
-            else if (!INJECT && expo > SPARC_EXPO_SAFE) { p_deb = 0.0; tiny = true; }
-            else p_deb = 1.0 / (1.0 + exp(expo));
-        }
-        (void)tiny;
-        double p_rnd;
-        if (gap >= P.random_short_max_gap) p_rnd = 0.0;
-        else if (gap <= P.random_short_min_gap) p_rnd = P.random_short_max_probability;
-        else {
-            double gf = 1.0 - (gap - P.random_short_min_gap) / (P.random_short_max_gap - P.random_short_min_gap);
-            p_rnd = gf * P.random_short_max_probability;
-        }
-        if (p_deb > 0.0 && draw(0) < p_deb) {
-            s.deb_short_rem = P.debris_short_duration;
-            is_short = true;
-            if (s.writer) S.stat_short_events[e] += 1;
-        } else if (p_rnd > 0.0 && draw(1) < p_rnd) {
-            s.rand_short_rem = P.random_short_duration;
-            is_short = true;
-            if (s.writer) S.stat_short_events[e] += 1;
-        }
-    }
-    if (is_short) s.voltage = 0.0;
-
-    // ---- state machine (ignition.py:186-195, 247-319) ----------------------------------------
-    bool fresh_spark = false;
-    if (s.spark_state == 0) {
-        if (is_short) {
-            s.spark_state = -1; s.flags &= ~SPARC_F_HAS_Y; s.spark_dur = 0;
-            if (s.writer) { S.stat_pulse_short[e] += 1; S.spark_y[e] = -1.0; }
-        } else {
-            s.voltage = s.tv_eff;
-            const double u3 = draw(2);
-            // get_lambda (ignition.py:348-364): ln2 / (a*gap^2 + b*gap + c), raw gap
-            double den = P.ignition_a_coeff * (gap_raw * gap_raw) + P.ignition_b_coeff * gap_raw + P.ignition_c_coeff;
-            if (u3 < 0.6931471805599453 / den) {
-                double y = 0.0 + (P.workpiece_height - 0.0) * draw(3);      // Generator.uniform
-                s.spark_state = 1; s.flags |= SPARC_F_HAS_Y; s.spark_dur = 0;
-                s.voltage = s.tv_eff * P.spark_voltage_factor;
-                s.win_sparks += 1;
-                fresh_spark = true;
-                s.plasma_idx = (P.segment_len != 0.0) ? P.zone_start + (int)py_floordiv(y, P.segment_len) : P.zone_start;
-                if (s.writer) { S.stat_sparks[e] += 1; S.spark_y[e] = y; }
-            }
-        }
-    } else if (s.spark_state == 1) {
-        s.spark_dur += 1;
-        if ((double)s.spark_dur >= s.on_eff) { s.spark_state = -2; if (!is_short) s.voltage = 0.0; }
-        else if (!is_short) s.voltage = s.tv_eff * P.spark_voltage_factor;
-    } else if (s.spark_state == -1) {
-        s.spark_dur += 1;
-        if ((double)s.spark_dur >= s.on_eff) s.spark_state = -2;
-    } else {  // -2 rest
-        s.spark_dur += 1;
-        if ((double)s.spark_dur >= s.onoff_eff) {
-            s.spark_state = 0; s.flags &= ~SPARC_F_HAS_Y; s.spark_dur = 0;
-            if (s.writer) S.spark_y[e] = -1.0;
-            if (!is_short) s.voltage = s.tv_eff;
-        } else if (!is_short) s.voltage = 0.0;
-    }
-    if (is_short) { s.flags |= SPARC_F_SHORT; s.win_short_us += 1; }
-    else s.flags &= ~SPARC_F_SHORT;
-    s.win_vsum += s.voltage;
-    // state.current is reassigned on every path above: Ipk in spark / short-pulse, else 0
-    const double current = (s.spark_state == 1 || s.spark_state == -1) ? s.ipk : 0.0;
-
-    // ---- MaterialRemovalModule.update (material.py:79-174) -----------------------------------
-    double crater_volume = 0.0;                             // state.last_crater_volume [mm^3]
-    if (fresh_spark) {
-        const int mode = (s.current_mode == 0) ? 1 : s.current_mode;       // material.py:104-105
-        if (mode < 1 || mode > SPARC_MAX_MODE || !P.crater_avail[mode]) {
-            s.flags |= SPARC_F_MODE_ERROR;                  // the reference raises ValueError here
-            s.became_done = true; s.thermal = false; s.freeze = true;
-            s.fast_ok = false;
-            return;
-        }
-        double z;
-        if (INJECT) z = draw(4);
-        else {
-            uint32_t w[4];
-            philox4x32_10(s.env_id, (uint32_t)s.time, s.episode, 4u, k0, k1, w);
-            z = sqrt(-2.0 * log(u01(w[0]))) * cospi(2.0 * u01(w[1]));
-        }
-        double vol_um3 = P.crater_mean[mode] + P.crater_std[mode] * z;
-        vol_um3 = (vol_um3 > 0.0) ? vol_um3 : 0.0;
-        crater_volume = vol_um3 / 1e9;
-        if (crater_volume > 0.0) {
-            double kh = P.kerf_times_height[mode];
-            double dx_um = 0.0;
-            if (kh > 0.0) dx_um = (crater_volume / kh) * 1000.0;
-            s.wp += dx_um;
-        }
-        if (s.writer) {
-            S.stat_crater_sum[e] += vol_um3;
-            S.last_crater_volume[e] = crater_volume;
-            if (s.current_mode != 0) S.mat_cached_mode[e] = mode;
-            S.mat_info_mode[e] = mode;
-        }
-    }
-
-    // ---- DielectricModule.update (dielectric.py:82-163) --------------------------------------
-    double gap_um = s.wp - s.wire;
-    gap_um = (gap_um > 0.001) ? gap_um : 0.001;
-    s.gap_prev = gap_um;
-    const double cavity_volume = P.cavity_volume_coeff * (gap_um * 0.001);
-    if (crater_volume > 0.0) {                              // fresh spark with a crater
-        s.debris_volume += crater_volume;
-        s.ion_end = s.time + P.ion_channel_duration;        // ion_rem = max(0, ion_end - time)
-    }
-    if (cavity_volume > 0.0) {
-        double d = s.debris_volume / cavity_volume;
-        s.debris_density = (d < 1.0) ? d : 1.0;
-    } else s.debris_density = 0.0;
-    s.dens_valid = true;
-    if (fabs(gap_um - s.d_last_gap) > 0.01 || fabs(s.debris_density - s.d_last_density) > 0.001) {
-        double r = gap_um / P.reference_gap;
-        double gf = r * r * r;                              // (gap/ref)**3
-        gf = (gf < 1.0) ? gf : 1.0;
-        double x = P.debris_obstruction_coeff * s.debris_density;
-        double df;
-        if (x < 0.5) df = (1.0 - 0.5 * x) / (1.0 + 0.5 * x);               // fast_exp Pade branch
-        else df = exp(-x);
-        s.flow = gf * df;
-        s.d_last_gap = gap_um;
-        s.d_last_density = s.debris_density;
-    }
-    s.pend_flush = true;                                    // flushing of this µs applied lazily
-
-    // ---- WireModule.update, host part (wire.py:259-309, 349-374) -----------------------------
-    if (fabs(s.flow - s.w_last_flow) > 0.01) {
-        double ve = P.convection_velocity_factor * S.unwind_v[e];
-        ve = (ve > -0.9) ? ve : -0.9;
-        double hb = P.base_convection_coefficient * (1.0 + ve);
-        double hfloor = 0.1 * P.base_convection_coefficient;
-        hb = (hb > hfloor) ? hb : hfloor;
-        double he = hb * (1.0 + P.convection_flow_enhancement * s.flow);
-        s.hb = (float)hb; s.he = (float)he; s.refresh = true;
-        if (s.writer) { S.h_base[e] = s.hb; S.h_enh[e] = s.he; }
-        s.w_last_flow = s.flow;
-    }
-    if (current * current > 1e-6) {                         // wire.py:98-102
-        const double f = P.temp_update_factor;
-        double jf = f * (P.joule_geom_factor * (current * current) * P.rho_elec);
-        s.jA = (float)(jf * P.alpha_rho);
-        s.jB = (float)(jf * (1.0 - P.alpha_rho * P.temp_ref));
-        s.heat_on = true;
-        if (s.spark_state == 1) {                           // plasma spot, wire.py:293-297
-            double ph = P.plasma_efficiency * s.voltage * current;
-            if (!isfinite(ph)) ph = 0.0;
-            s.fP = (float)(f * ph);
-        }
-    }
-    prepare_fast(s, P);
-}
-
-// resident blocks per SM the register budget is sized for (65536 regs / (128 thr * blocks))
+// resident blocks per SM the register budget is sized for
 #ifndef SPARC_MINB_SMALL
 #define SPARC_MINB_SMALL 4
 #endif
-#ifndef SPARC_MINB_MID
-#define SPARC_MINB_MID 3
-#endif
-#ifndef SPARC_MINB_BIG
-#define SPARC_MINB_BIG 2
-#endif
-constexpr int min_blocks_for(int K) { return K <= 13 ? SPARC_MINB_SMALL : (K <= 20 ? SPARC_MINB_MID : SPARC_MINB_BIG); }
+constexpr int min_blocks_for(int K) { return K <= 13 ? SPARC_MINB_SMALL : (K <= 20 ? 3 : 2); }
 
-template <int K, int L, bool INJECT>
+#define SPARC_LN2_UP 0.6931471805599460    /* ln2*(1+2^-50): u3 < fl(ln2/den) implies u3*den <= this */
+
+template <int K, bool INJECT>
 __global__ void __launch_bounds__(SPARC_BLOCK_THREADS, min_blocks_for(K))
 step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
-            const __grid_constant__ StepArgs a)
+             const __grid_constant__ StepArgs a)
 {
     constexpr unsigned FULL = 0xffffffffu;
-    constexpr int G = 32 / L;
+    constexpr int WPB = SPARC_BLOCK_THREADS / 32;
+    __shared__ double sm_post[WPB][32];
     const int lane = threadIdx.x & 31;
-    const int sub = lane % L;
-    const int grp = lane / L;
-    const int env = (blockIdx.x * (SPARC_BLOCK_THREADS / 32) + (threadIdx.x >> 5)) * G + grp;
-    const bool valid = env < a.n_envs;
-    const int e = valid ? env : 0;
+    const int wib = threadIdx.x >> 5;
+    const int e = blockIdx.x * WPB + wib;
+    if (e >= a.n_envs) return;                  // whole warp; no block-level barrier is used
+    double *post_s = sm_post[wib];
+    const uint32_t k0 = (uint32_t)a.seed, k1 = (uint32_t)(a.seed >> 32);
 
-    // ---------------- load: cold state into the local-memory struct, hot state into registers --
+    // ---------------- load ---------------------------------------------------------------------
     EnvState s;
-    s.e = e; s.it = 0; s.writer = valid && sub == 0;
+    s.e = e; s.it = 0; s.writer = lane == 0;
     s.env_id = a.env_id_base + (uint32_t)e;
     s.episode = (uint32_t)S.episode[e];
     s.debris_density = S.debris_density[e]; s.flow = S.flow[e];
@@ -472,14 +202,17 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     if (spark_state == 1 && (flags & SPARC_F_HAS_Y))
         s.plasma_idx = (P.segment_len != 0.0) ? P.zone_start + (int)py_floordiv(S.spark_y[e], P.segment_len) : P.zone_start;
 
-    // fast-path constants mirrored in registers (refreshed after every general µs)
-    double gap_lo_f = 0.0, gap_hi_f = -1.0, lo_c = 0.0, hi_c = 0.0, flush_amt = 0.0, tv_eff = s.tv_eff;
-    int next_latch = s.latch_time + P.servo_interval, onoff_thr = s.onoff_thr;
-    bool fast_ok = false, ran_fast = false, first = true, zone_mean_written = false;
+    if (flags & SPARC_F_DONE) {                 // terminated envs are left untouched
+        if (s.writer) { S.win_vsum[e] = 0.0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0; }
+        return;
+    }
+
+    int next_latch = s.latch_time + P.servo_interval;
+    bool fast_ok = false, ran_fast = false, zone_mean_written = false, done = false;
     int tsi_break = -1;
 
-    // upper bound of the ignition probability lambda(gap) = ln2/(a g^2 + b g + c) over all gaps
-    // (ignition.py:348-364): a draw above it can never ignite, whatever the gap.
+    // upper bound of lambda(gap) = ln2/(a g^2 + b g + c) over all gaps (ignition.py:348-364): a
+    // draw above it can never ignite, whatever the gap.
     double lam_bound = 2.0;
     if (P.ignition_a_coeff > 0.0) {
         double den_min = P.ignition_c_coeff - P.ignition_b_coeff * P.ignition_b_coeff / (4.0 * P.ignition_a_coeff);
@@ -488,19 +221,20 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     uint32_t w_thresh = 0xffffffffu;            // word >= w_thresh  =>  u01(word) >= lam_bound
     if (lam_bound < 0.999) w_thresh = (uint32_t)(lam_bound * 4294967296.0) + 2u;
 
-    const bool done_at_entry = !valid || (flags & SPARC_F_DONE) != 0;
-    bool done = done_at_entry;
-
     // ---------------- temperature field -> registers -----------------------------------------
     const int N = P.n_segments;
     const int M = N - 1;                        // dynamic cells 1..N-1; cell 0 == spool_T
-    const float spoolf = (float)P.spool_T;
-    float T[K];
+    float spoolf = (float)P.spool_T;
+    asm volatile("" : "+f"(spoolf));            // keep it in a register (no per-µs F2F rematerialisation)
+    static_assert(K % 2 == 0, "packed stencil needs an even number of cells per lane");
+    constexpr int H = K / 2;
+    float2 T[H];                                // T[j] = (cell j, cell j+H) of this lane's K slots
     float *Trow = S.T + (size_t)e * S.n_pad;
 #pragma unroll
-    for (int j = 0; j < K; j++) {
-        int sl = sub * K + j;
-        T[j] = (sl < M) ? Trow[sl + 1] : spoolf;
+    for (int j = 0; j < H; j++) {
+        const int sa = lane * K + j, sb = sa + H;
+        T[j].x = (sa < M) ? Trow[sa + 1] : spoolf;
+        T[j].y = (sb < M) ? Trow[sb + 1] : spoolf;
     }
 
     // ---------------- stencil coefficients ---------------------------------------------------
@@ -514,235 +248,279 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         cRf = (float)(f * P.k_cond_coeff);
         ncL = -(float)(f * (P.k_cond_coeff + adv));
     }
-    float cE[K], c0[K], cR[K];
+    float2 cE[H], c0[H], cR[H];
+    bool convex = false;                        // T' is a convex combination of T, T_diel (no source)
+    auto slot_coeffs = [&](int sl, float hb, float he, float &e_, float &z_, float &r_) {
+        const int i = sl + 1;
+        if (sl < M) {
+            float h = (i >= P.actual_zone_start && i < P.actual_zone_end) ? he : hb;
+            double hA = (double)h * P.A;        // conv_coeff, wire.py:110
+            e_ = (float)(-(f * hA));
+            z_ = (float)(f * hA * P.dielectric_temperature);
+            r_ = (i < N - 1) ? cRf : 0.0f;      // Neumann end, wire.py:95
+        } else {                                // pad slot: pinned near spool_T, feeds nothing
+            e_ = -1.0f;
+            z_ = spoolf;
+            r_ = 0.0f;
+        }
+    };
     auto refresh_coeffs = [&](float hb, float he) {
 #pragma unroll
-        for (int j = 0; j < K; j++) {
-            int sl = sub * K + j;
-            int i = sl + 1;
-            if (sl < M) {
-                float h = (i >= P.actual_zone_start && i < P.actual_zone_end) ? he : hb;
-                double hA = (double)h * P.A;    // conv_coeff, wire.py:110
-                cE[j] = (float)(-(f * hA));
-                c0[j] = (float)(f * hA * P.dielectric_temperature);
-                cR[j] = (i < N - 1) ? cRf : 0.0f;     // Neumann end, wire.py:95
-            } else {                            // pad slot: pinned near spool_T, feeds nothing
-                cE[j] = -1.0f;
-                c0[j] = spoolf;
-                cR[j] = 0.0f;
-            }
+        for (int j = 0; j < H; j++) {
+            slot_coeffs(lane * K + j, hb, he, cE[j].x, c0[j].x, cR[j].x);
+            slot_coeffs(lane * K + j + H, hb, he, cE[j].y, c0[j].y, cR[j].y);
         }
-    };
-    auto freeze = [&]() {                       // env finished: make the stencil a no-op
-#pragma unroll
-        for (int j = 0; j < K; j++) { cE[j] = 0.0f; c0[j] = 0.0f; cR[j] = 0.0f; }
-        ncL = 0.0f;
+        const float hmax = fmaxf(hb, he), hmin = fminf(hb, he);
+        const float ce_max = (float)(f * ((double)hmax * P.A));
+        convex = hmin >= 0.0f && cRf >= 0.0f && ncL <= 0.0f && (cRf - ncL + ce_max) <= 0.999f &&
+                 fmaxf((float)P.dielectric_temperature, spoolf) < P.critical_temperature_f32 - 1.0f;
     };
     refresh_coeffs(S.h_base[e], S.h_enh[e]);
-    if (done) freeze();
+    bool cold_ok = false;                       // max T < critical - 1 K after the last executed µs
 
     // contact span in slot coordinates of this lane
-    const int j_span_lo = P.contact_bottom_idx - 1 - sub * K;
-    const int j_span_hi = P.contact_top_idx - 1 - sub * K;
-
-    // Philox cache for the ignition roll (slot 2): one call serves 4 consecutive µs
-    uint32_t u3w[4] = {0, 0, 0, 0};
-    uint32_t u3_block = 0xffffffffu;
+    const int j_span_lo = P.contact_bottom_idx - 1 - lane * K;
+    const int j_span_hi = P.contact_top_idx - 1 - lane * K;
     const double *drow = INJECT ? a.draws + (size_t)e * a.n_us * SPARC_N_DRAW_SLOTS : nullptr;
 
-    for (int it = 0; it < a.n_us; ++it) {
-        if (__all_sync(FULL, done)) break;
-        bool thermal = false;                   // this env runs the thermal update this µs
-        bool heat_on = false, quiet = false;
-        if (!done) {
-            // ================= quiet-µs fast path =============================================
-            // Idle / rest µs with no latch, no short circuit, no ignition and no hysteresis
-            // refresh: every reference branch is resolved by a few comparisons against bounds
-            // precomputed in prepare_fast(); anything else falls through to general_pre().
-            const double g = wp - wire;
-            const double deb_new = (debris_volume > 0.001) ? debris_volume - flush_amt : debris_volume;
-            quiet = fast_ok && !first && time < next_latch && (spark_state == 0 || spark_state == -2) &&
-                    g >= gap_lo_f && g <= gap_hi_f && deb_new >= lo_c * g && deb_new <= hi_c * g;
-            if (INJECT && quiet) quiet = drow[(size_t)it * SPARC_N_DRAW_SLOTS + 0] >= SPARC_U1_SAFE;
-            if (quiet && spark_state == 0) {
-                double u3;
-                bool maybe;
-                if (INJECT) {
-                    u3 = drow[(size_t)it * SPARC_N_DRAW_SLOTS + 2];
-                    maybe = !(u3 >= lam_bound);
-                } else {
-                    const uint32_t blk = (uint32_t)time >> 2;
-                    if (blk != u3_block) {
-                        philox4x32_10(s.env_id, blk, s.episode, 2u, (uint32_t)a.seed, (uint32_t)(a.seed >> 32), u3w);
-                        u3_block = blk;
-                    }
-                    const uint32_t w = pick4(u3w, time & 3);
-                    maybe = w < w_thresh;
-                    u3 = u01(w);
-                }
-                if (maybe) {
-                    // u3 < fl(ln2/den) can only hold if u3*den <= ln2*(1+2^-50)
-                    double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
-                    maybe = !(den > 0.0 && u3 * den > 0.6931471805599460);
-                }
-                quiet = !maybe;
-            }
-            if (quiet) {
-                debris_volume = deb_new;
-                gap_prev = g;
-                ran_fast = true;
-                if (spark_state == 0) voltage = tv_eff;
-                else {
-                    const int nd = spark_dur + 1;
-                    if (nd >= onoff_thr) {      // rest -> idle (ignition.py:307-314)
-                        spark_state = 0; spark_dur = 0; flags &= ~SPARC_F_HAS_Y;
-                        voltage = tv_eff;
-                        if (s.writer) S.spark_y[e] = -1.0;
-                    } else { spark_dur = nd; voltage = 0.0; }
-                }
-                win_vsum += voltage;
-                thermal = true;
-            } else {
-                // ================= general µs ==================================================
-                s.wp = wp; s.wire = wire; s.v = v; s.prev_accel = prev_accel; s.target_delta = target_delta;
-                s.voltage = voltage; s.debris_volume = debris_volume; s.win_vsum = win_vsum; s.gap_prev = gap_prev;
-                s.time = time; s.spark_state = spark_state; s.spark_dur = spark_dur; s.flags = flags;
-                s.it = it;
-                if (ran_fast) { s.dens_valid = false; s.pend_flush = true; ran_fast = false; }
-                general_pre<INJECT>(s, P, S, a);
-                wp = s.wp; target_delta = s.target_delta; voltage = s.voltage; debris_volume = s.debris_volume;
-                win_vsum = s.win_vsum; gap_prev = s.gap_prev;
-                spark_state = s.spark_state; spark_dur = s.spark_dur; flags = s.flags;
-                gap_lo_f = s.gap_lo_f; gap_hi_f = s.gap_hi_f; lo_c = s.lo_c; hi_c = s.hi_c;
-                flush_amt = s.flush_amt; tv_eff = s.tv_eff; onoff_thr = s.onoff_thr;
-                next_latch = s.latch_time + P.servo_interval;
-                fast_ok = s.fast_ok;
-                first = false;
-                thermal = s.thermal;
-                heat_on = s.heat_on;
-                if (s.refresh) refresh_coeffs(s.hb, s.he);
-                if (s.freeze) { done = true; freeze(); }
+    int it = 0;
+    while (it < a.n_us && !done) {
+        // ================= block setup: mechanics look-ahead ==================================
+        int nb = a.n_us - it;
+        if (nb > 32) nb = 32;
+        int to_latch = next_latch - time;
+        double delta_blk = target_delta;
+        bool force_general = false;
+        if (to_latch <= 0) {                    // the first µs of this block latches the action
+            delta_blk = (double)a.act.servo[e];
+            to_latch = (P.servo_interval > 1) ? P.servo_interval : 1;
+            force_general = true;
+        }
+        if (nb > to_latch) nb = to_latch;       // a block never straddles a latch
+        const double wire_b = wire;
+        s.blk_wire = wire; s.blk_v = v; s.blk_pa = prev_accel;
+        __syncwarp();
+        if (!mech_block_noclip(P, wire, v, prev_accel, delta_blk, nb, post_s, lane == 0)) {
+            wire = s.blk_wire; v = s.blk_v; prev_accel = s.blk_pa;     // a clip was active: exact path
+#pragma unroll 1
+            for (int k = 0; k < nb; k++) {
+                mech_step(P, wire, v, prev_accel, delta_blk);
+                if (lane == 0) post_s[k] = wire;
             }
         }
+        __syncwarp();
+        const double post_l = post_s[(lane < nb) ? lane : nb - 1];      // wire after µs `lane`
+        double pre_l = __shfl_up_sync(FULL, post_l, 1);                  // wire before µs `lane`
+        if (lane == 0) pre_l = wire_b;
+        // ignition roll of µs `lane` (slot 2): word (time+lane)&3 of Philox block (time+lane)>>2
+        uint32_t w_l = 0;
+        if (!INJECT) {
+            const uint32_t tl = (uint32_t)(time + lane);
+            uint32_t w[4];
+            philox4x32_10(s.env_id, tl >> 2, s.episode, 2u, k0, k1, w);
+            w_l = pick4(w, tl & 3);
+        }
+        // finished inside this block: exact mechanics state after `steps` µs of it
+        auto rewind_mech = [&](int steps) {
+            wire = s.blk_wire; v = s.blk_v; prev_accel = s.blk_pa;
+#pragma unroll 1
+            for (int k = 0; k < steps; k++) mech_step(P, wire, v, prev_accel, delta_blk);
+        };
 
-        // ---- compute_thermal_update (wire.py:58-123): convergent, all lanes ------------------
-        float left = __shfl_up_sync(FULL, T[K - 1], 1, L);
-        float right = __shfl_down_sync(FULL, T[0], 1, L);
-        if (sub == 0) left = spoolf;
-        float acc[K];
-#pragma unroll
-        for (int j = 0; j < K; j++) acc[j] = fmaf(cE[j], T[j], c0[j]);
-        if (heat_on) {
-            const float jA = s.jA, jB = s.jB, fP = s.fP;
-            const int jp = (s.spark_state == 1 && s.plasma_idx >= 0 && s.plasma_idx < N) ? s.plasma_idx - 1 - sub * K
-                                                                                         : -(1 << 20);
-#pragma unroll
-            for (int j = 0; j < K; j++) {
-                if (j >= j_span_lo && j <= j_span_hi) acc[j] += fmaf(jA, T[j], jB);
-                if (j == jp) acc[j] += fP;
-            }
-        }
-        float lmax = spoolf;
-        {
-            float dprev = T[0] - left;
-#pragma unroll
-            for (int j = 0; j < K; j++) {
-                float dnext = ((j + 1 < K) ? T[j + 1] : right) - T[j];
-                float q = fmaf(cR[j], dnext, acc[j]);
-                q = fmaf(ncL, dprev, q);
-                dprev = dnext;
-                T[j] = T[j] + q;
-                lmax = fmaxf(lmax, T[j]);
-            }
-        }
-        // ---- _check_wire_breaking (wire.py:376-388): warp vote --------------------------------
-        const unsigned hot_b = __ballot_sync(FULL, lmax > P.critical_temperature_f32);
-        unsigned brk_b = 0;
-        if (hot_b) brk_b = __ballot_sync(FULL, lmax > P.breaking_temperature_f32);
-        // zone mean (wire.py:338-347, 390-394), only when enabled
-        if (P.compute_zone_mean) {
-            bool need_zm = false;
-            if (thermal) {
-                w_zone_counter += 1;
-                need_zm = w_zone_counter >= P.zone_mean_interval;
-            }
-            if (__any_sync(FULL, need_zm)) {
-                int za = P.actual_zone_start, zb = P.actual_zone_end;
-                if (!(zb > za && zb <= N)) { za = 0; zb = N; }
-                float part = 0.0f;
-#pragma unroll
-                for (int j = 0; j < K; j++) {
-                    int i = sub * K + j + 1;
-                    if (i >= za && i < zb) part += T[j];
+        int i = 0;
+        while (i < nb) {
+            // ================= look-ahead: length of the quiet run starting at µs i ===========
+            int n = 0;
+            int off_tr = -1;                    // run offset of the rest -> idle transition µs
+            const double g = wp - pre_l;
+            if (!force_general && fast_ok && (spark_state == 0 || spark_state == -2)) {
+                const int off = lane - i;
+                bool ok = lane < nb && g >= s.gap_lo_f && g <= s.gap_hi_f;
+                // debris after at most off+1 deferred flushes (sequential rounding <= 32 ulp(1))
+                double deb_lo = debris_volume;
+                if (debris_volume > 0.001) deb_lo = debris_volume - (double)(off + 1) * s.flush_amt - 1e-14;
+                ok = ok && deb_lo >= s.lo_c * g && debris_volume <= s.hi_c * g;
+                ok = ok && !(post_l > wp + 100.0);              // collision µs (wire_edm.py:173-175)
+                if (spark_state == -2) {
+                    off_tr = s.onoff_thr - spark_dur - 1;
+                    if (off_tr < 0) off_tr = 0;
                 }
-                if (sub == 0 && za == 0) part += spoolf;     // cell 0 when the zone starts at 0
-                double tot = (double)part;
+                if (P.compute_zone_mean) ok = ok && (w_zone_counter + off + 1 < P.zone_mean_interval);
+                if (INJECT) {
+                    if (lane < nb) {
+                        const double *d = drow + (size_t)(it + lane) * SPARC_N_DRAW_SLOTS;
+                        ok = ok && d[0] >= SPARC_U1_SAFE;
+                        if (off > off_tr) {
+                            const double u3 = d[2];
+                            if (!(u3 >= lam_bound)) {
+                                double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
+                                ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
+                            }
+                        }
+                    }
+                } else if (off > off_tr && w_l < w_thresh) {
+                    // u3 < fl(ln2/den) can only hold if u3*den <= ln2*(1+2^-50)
+                    const double u3 = u01(w_l);
+                    double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
+                    ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
+                }
+                const unsigned stop = __ballot_sync(FULL, !ok) >> i;
+                n = stop ? __ffs(stop) - 1 : 32 - i;
+            }
+            force_general = false;
+
+            if (n > 0) {
+                // ================= quiet run ===================================================
+                bool broke = false;
+                int nx;
+                if (cold_ok && convex)
+                    nx = run_quiet<H, false>(T, cE, c0, cR, ncL, spoolf, lane, n, 0.f, 0.f, crit_count, broke, cold_ok);
+                else
+                    nx = run_quiet<H, true>(T, cE, c0, cR, ncL, spoolf, lane, n, P.critical_temperature_f32,
+                                            P.breaking_temperature_f32, crit_count, broke, cold_ok);
+                // scalar bookkeeping of the nx quiet µs (ignition.py:302-319, dielectric.py:104-144)
+                int n_idle = nx;
+                if (spark_state == -2) {
+                    if (nx > off_tr) {          // rest -> idle on run offset off_tr
+                        spark_state = 0; spark_dur = 0; flags &= ~SPARC_F_HAS_Y;
+                        if (s.writer) S.spark_y[e] = -1.0;
+                        n_idle = nx - off_tr;
+                    } else { spark_dur += nx; n_idle = 0; }
+                }
+                voltage = (n_idle > 0) ? s.tv_eff : 0.0;
+                win_vsum += (double)n_idle * s.tv_eff;
+                if (debris_volume > 0.001 && s.flush_amt > 0.0) {
+#pragma unroll 1
+                    for (int k = 0; k < nx && debris_volume > 0.001; k++) debris_volume = debris_volume - s.flush_amt;
+                }
+                gap_prev = __shfl_sync(FULL, g, i + nx - 1);
+                ran_fast = true;
+                if (P.compute_zone_mean) w_zone_counter += nx;
+                if (broke) {                    // wire_edm.py:129-130 on the last µs of the run
+                    flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
+                    tsi_break = 0;
+                    done = true;
+                    time += nx - 1;
+                    rewind_mech(i + nx - 1);
+                    break;
+                }
+                time += nx;
+                i += nx;
+                continue;
+            }
+
+            // ================= general µs ======================================================
+            s.wp = wp; s.wire = __shfl_sync(FULL, pre_l, i); s.v = 0.0; s.prev_accel = 0.0;
+            s.target_delta = target_delta;
+            s.voltage = voltage; s.debris_volume = debris_volume; s.win_vsum = win_vsum; s.gap_prev = gap_prev;
+            s.time = time; s.spark_state = spark_state; s.spark_dur = spark_dur; s.flags = flags;
+            s.it = it + i;
+            if (ran_fast) { s.dens_valid = false; s.pend_flush = true; ran_fast = false; }
+            general_pre<INJECT>(s, P, S, a);
+            wp = s.wp; target_delta = s.target_delta; voltage = s.voltage; debris_volume = s.debris_volume;
+            win_vsum = s.win_vsum; gap_prev = s.gap_prev;
+            spark_state = s.spark_state; spark_dur = s.spark_dur; flags = s.flags;
+            next_latch = s.latch_time + P.servo_interval;
+            fast_ok = s.fast_ok;
+            if (s.refresh) refresh_coeffs(s.hb, s.he);
+            if (s.freeze) {                     // crater-table miss: frozen before the thermal update
+                done = true;
+                rewind_mech(i);
+                break;
+            }
+            // ---- compute_thermal_update with sources (wire.py:58-123) -------------------------
+            float lmax = spoolf;
+            {
+                float left = __shfl_up_sync(FULL, T[H - 1].y, 1);
+                const float right = __shfl_down_sync(FULL, T[0].x, 1);
+                if (lane == 0) left = spoolf;
+                float2 acc[H];
 #pragma unroll
-                for (int o = L / 2; o > 0; o >>= 1) tot += __shfl_xor_sync(FULL, tot, o, L);
-                if (need_zm) {
+                for (int j = 0; j < H; j++) acc[j] = __ffma2_rn(cE[j], T[j], c0[j]);
+                if (s.heat_on) {
+                    const float jA = s.jA, jB = s.jB, fP = s.fP;
+                    const int jp = (s.spark_state == 1 && s.plasma_idx >= 0 && s.plasma_idx < N)
+                                       ? s.plasma_idx - 1 - lane * K : -(1 << 20);
+#pragma unroll
+                    for (int j = 0; j < H; j++) {
+                        if (j >= j_span_lo && j <= j_span_hi) acc[j].x += fmaf(jA, T[j].x, jB);
+                        if (j == jp) acc[j].x += fP;
+                        if (j + H >= j_span_lo && j + H <= j_span_hi) acc[j].y += fmaf(jA, T[j].y, jB);
+                        if (j + H == jp) acc[j].y += fP;
+                    }
+                }
+                const float2 ncL2 = make_float2(ncL, ncL);
+                float2 dprev = sub2(T[0], make_float2(left, T[H - 1].x));
+                const float2 last_next = make_float2(T[0].y, right);
+#pragma unroll
+                for (int j = 0; j < H; j++) {
+                    const float2 dnext = sub2((j + 1 < H) ? T[j + 1] : last_next, T[j]);
+                    float2 q = __ffma2_rn(cR[j], dnext, acc[j]);
+                    q = __ffma2_rn(ncL2, dprev, q);
+                    dprev = dnext;
+                    T[j] = __fadd2_rn(T[j], q);
+                    lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
+                }
+            }
+            // ---- _check_wire_breaking (wire.py:376-388) ---------------------------------------
+            cold_ok = !__any_sync(FULL, lmax > P.critical_temperature_f32 - 1.0f);
+            bool hot = false, brk = false;
+            if (!cold_ok) {
+                hot = __any_sync(FULL, lmax > P.critical_temperature_f32);
+                if (hot) brk = __any_sync(FULL, lmax > P.breaking_temperature_f32);
+            }
+            crit_count = hot ? crit_count + 1 : 0;
+            // zone mean (wire.py:338-347, 390-394), only when enabled
+            if (P.compute_zone_mean) {
+                w_zone_counter += 1;
+                if (w_zone_counter >= P.zone_mean_interval) {
+                    int za = P.actual_zone_start, zb = P.actual_zone_end;
+                    if (!(zb > za && zb <= N)) { za = 0; zb = N; }
+                    float part = 0.0f;
+#pragma unroll
+                    for (int jj = 0; jj < K; jj++) {     // ascending cell order within the lane
+                        int c = lane * K + jj + 1;
+                        if (c >= za && c < zb) part += (jj < H) ? T[jj].x : T[jj - H].y;
+                    }
+                    if (lane == 0 && za == 0) part += spoolf;    // cell 0 when the zone starts at 0
+                    double tot = (double)part;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(FULL, tot, o);
                     double zm = (double)(float)(tot / (double)(zb - za));
                     if (s.writer) { S.w_last_zone_mean[e] = zm; S.wire_avg_T[e] = zm; }
                     zone_mean_written = true;
                     w_zone_counter = 0;
                 }
             }
-        }
-        if (thermal) {
-            const unsigned gmask = group_mask<L>(grp);
-            crit_count = (hot_b & gmask) ? crit_count + 1 : 0;
-            if (brk_b & gmask) {
+            if (brk) {
                 // wire_edm.py:129-130: early return, no mechanics, no time bookkeeping
                 flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
-                tsi_break = quiet ? 0 : s.tsi_prev;
+                tsi_break = s.tsi_prev;
                 done = true;
-                freeze();
-            } else {
-                // ---- MechanicsModule.update (mechanics.py:79-114) -----------------------------
-                double a_nom;
-                if (P.control_mode == 0) {
-                    double x_err = wire - (wire + target_delta);
-                    a_nom = P.damping_coeff * v + P.stiffness_coeff * x_err;
-                } else {
-                    a_nom = -P.omega_n * (v - target_delta);
-                }
-                double da = a_nom - prev_accel;
-                if (fabs(a_nom) <= P.max_acceleration && fabs(da) <= P.max_jerk_dt) {
-                    prev_accel = prev_accel + da;           // no clip active
-                } else {
-                    if (a_nom > P.max_acceleration) a_nom = P.max_acceleration;
-                    else if (a_nom < -P.max_acceleration) a_nom = -P.max_acceleration;
-                    da = a_nom - prev_accel;
-                    if (da > P.max_jerk_dt) da = P.max_jerk_dt;
-                    else if (da < -P.max_jerk_dt) da = -P.max_jerk_dt;
-                    prev_accel = prev_accel + da;
-                }
-                v += prev_accel * P.mech_dt;
-                if (!(fabs(v) <= P.max_speed)) {
-                    if (v > P.max_speed) v = P.max_speed;
-                    else if (v < -P.max_speed) v = -P.max_speed;
-                }
-                wire += v * P.mech_dt;
-                // ---- time bookkeeping (wire_edm.py:134-144): t_servo, t_spark_end are time-based
-                time += 1;
-                if (!quiet && spark_state == 1) s.tse_ref = time;
-                // ---- _check_termination (wire_edm.py:172-179) ---------------------------------
-                if (wire > wp + 100.0) { flags |= SPARC_F_BROKEN; done = true; freeze(); }
-                else if (!quiet && wp >= P.target_position) { flags |= SPARC_F_TARGET; done = true; freeze(); }
+                rewind_mech(i);
+                break;
             }
+            // mechanics of this µs is post_l of lane i; time bookkeeping (wire_edm.py:134-144)
+            time += 1;
+            if (spark_state == 1) s.tse_ref = time;
+            // ---- _check_termination (wire_edm.py:172-179) -------------------------------------
+            const double wire_after = __shfl_sync(FULL, post_l, i);
+            if (wire_after > wp + 100.0) { flags |= SPARC_F_BROKEN; done = true; }
+            else if (wp >= P.target_position) { flags |= SPARC_F_TARGET; done = true; }
+            if (done) { rewind_mech(i + 1); break; }
+            i += 1;
         }
+        it += nb;
     }
 
-    if (done_at_entry) {
-        if (s.writer) { S.win_vsum[e] = 0.0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0; }
-        return;
-    }
     // ---------------- store ------------------------------------------------------------------
 #pragma unroll
-    for (int j = 0; j < K; j++) {
-        int sl = sub * K + j;
-        if (sl < M) Trow[sl + 1] = T[j];
+    for (int j = 0; j < H; j++) {
+        const int sa = lane * K + j, sb = sa + H;
+        if (sa < M) Trow[sa + 1] = T[j].x;
+        if (sb < M) Trow[sb + 1] = T[j].y;
     }
-    if (sub == 0) {
+    if (lane == 0) {
         const bool thermal_break = (flags & SPARC_F_THERMAL_BREAK) != 0 && tsi_break >= 0;   // broke in THIS call
         const int win_steps = (time - time0) + (thermal_break ? 1 : 0);
         if (win_steps > 0 || (flags & SPARC_F_MODE_ERROR)) {

@@ -1,7 +1,7 @@
 #!/bin/bash
-# usage: tools/exp_bench.sh label [ENV=VAL ...] -- runs bench at 4096 and 16384 envs, prints value
+# usage: tools/exp_bench.sh label [ENV=VAL ...] -- runs bench at several env counts, prints value
 label=$1; shift
-for E in 4096 16384; do
+for E in ${EXP_ENVS:-4096 16384}; do
   env "$@" python bench.py --steps 10 --warmup 3 --no-cpu-baseline --envs-per-gpu $E 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$label', $E, '%.3e'%d['value'], 'ms/step %.3f'%d['ms_per_step'], d['config']['launch'])"
