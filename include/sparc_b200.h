@@ -143,6 +143,17 @@ int sparc_step(void *state, const SparcParams *p, const SparcActions *actions, i
 int sparc_step_injected(void *state, const SparcParams *p, const SparcActions *actions, int n_envs,
                         int n_us, const double *draws_dev, void *stream);
 
+/* Same as sparc_step (draws_dev == NULL) or sparc_step_injected (draws_dev != NULL), and the wire
+ * temperature field of envs 0..n_log_envs-1 is sampled every `log_every` µs of this call into
+ * tlog_dev[n_log_envs][n_us / log_every][n_segments] float32 — the reference's
+ * SimulationLogger("wire_temperature", interval) array layout (n_timesteps, n_segments)
+ * (utils/logger.py:128-150, experiments/animate_wire_heating.py:44-47).  Row r is the field after µs
+ * (r+1)*log_every - 1; rows at or after an env's termination hold its final field; envs already
+ * terminated at entry leave their rows untouched. */
+int sparc_step_logged(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+                      uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *tlog_dev, int log_every,
+                      int n_log_envs, void *stream);
+
 /* Observation summary of the last step call, obs_dev[SPARC_N_OBS][n_envs] float32:
  * 0 gap [µm], 1 wire_velocity [µm/s], 2 mean voltage over the call [V], 3 sparks ignited in the
  * call, 4 short-circuit µs in the call, 5 max wire temperature [K], 6 debris_density, 7 flags. */

@@ -94,6 +94,16 @@ CASES = {
     "thick_fine": dict(config=dict(workpiece_height=50.0, wire_diameter=0.25, target_cutting_distance=800.0),
                        mode="position", wire=dict(segment_len=0.1),
                        actions=[[0.0, 80.0, 13, 3.0, 30.0]], tape=("philox", 15), n_us=6000),
+    # BASELINE cfg 5: 50 mm workpiece, 0.05 mm segments (N=2200, 4 warps per env) and 0.02 mm segments
+    # (N=5500, 8 warps per env), I13 ON 3 / OFF 30, a few forced sparks so the field is not flat
+    "thick_2200": dict(config=dict(workpiece_height=50.0, wire_diameter=0.25, target_cutting_distance=800.0),
+                       mode="position", wire=dict(segment_len=0.05),
+                       actions=[[0.0, 80.0, 13, 3.0, 30.0]], tape=("philox_forced", (31, (40, 400, 1300, 2100, 3300))),
+                       n_us=4000),
+    "thick_5500": dict(config=dict(workpiece_height=50.0, wire_diameter=0.25, target_cutting_distance=800.0),
+                       mode="position", wire=dict(segment_len=0.02, compute_zone_mean=True, zone_mean_interval=250),
+                       actions=[[0.0, 80.0, 13, 3.0, 30.0]], tape=("philox_forced", (32, (25, 500, 1200, 2600))),
+                       n_us=3000),
     # deterministic KAT (i): single forced spark, no unwinding (single_spark_animation.py:214-249)
     "kat_single_spark": dict(config=README_CFG, mode="position", actions=[[0.0, 80.0, 5, 3.0, 80.0]],
                              tape=("never", (50,)), n_us=3000, unwind_v=0.0),
@@ -111,6 +121,8 @@ def case_tape(case: dict) -> np.ndarray:
     n = case["n_us"]
     if kind == "philox":
         return make_tape(arg, n)
+    if kind == "philox_forced":
+        return make_tape(arg[0], n, forced_ignitions=arg[1])
     if kind == "never":
         return never_ignite_tape(n, ignite_at=arg)
     raise ValueError(kind)

@@ -172,26 +172,42 @@ using StepFn = void (*)(const SparcParams, const SparcStatePtrs, const sparc::St
 
 struct Variant {
     int K;           // cells per lane (even: the stencil is two-wide)
+    int W;           // warps per environment (1: warp per env, 4 envs per block; > 1: block per env)
     StepFn fn[2];    // [INJECT]
 };
 
-#define VARIANT(K) {K, {sparc::step_kernel<K, false>, sparc::step_kernel<K, true>}}
+#define VARIANT(K, W) {K, W, {sparc::step_kernel<K, false, W>, sparc::step_kernel<K, true, W>}}
 const Variant kVariants[] = {
-    VARIANT(4), VARIANT(8), VARIANT(12), VARIANT(14), VARIANT(16), VARIANT(20), VARIANT(24), VARIANT(28), VARIANT(36),
+    VARIANT(4, 1),  VARIANT(8, 1),  VARIANT(12, 1), VARIANT(14, 1), VARIANT(16, 1), VARIANT(20, 1), VARIANT(24, 1),
+    VARIANT(16, 2), VARIANT(20, 2), VARIANT(24, 2),
+    VARIANT(16, 4), VARIANT(20, 4), VARIANT(24, 4),
+    VARIANT(16, 8), VARIANT(20, 8), VARIANT(24, 8),
 };
 constexpr int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
 
-// smallest variant whose 32 lanes x K slots hold the n_segments-1 dynamic cells
+// fewest warps per env, then fewest cells per lane, whose 32*W*K slots hold the n_segments-1 dynamic cells
 const Variant *pick_variant(int n_segments)
 {
     const int M = n_segments - 1;
     const Variant *best = nullptr;
     for (int i = 0; i < kNumVariants; i++) {
         const Variant &v = kVariants[i];
-        if (v.K * 32 < M) continue;
-        if (!best || v.K < best->K) best = &v;
+        if (v.K * 32 * v.W < M) continue;
+        if (!best || v.W < best->W || (v.W == best->W && v.K < best->K)) best = &v;
     }
     return best;
+}
+
+void launch_geometry(const Variant *v, int n_envs, int *blocks, int *threads)
+{
+    if (v->W == 1) {
+        const int wpb = SPARC_BLOCK_THREADS / 32;
+        *threads = SPARC_BLOCK_THREADS;
+        *blocks = (n_envs + wpb - 1) / wpb;
+    } else {
+        *threads = 32 * v->W;
+        *blocks = n_envs;
+    }
 }
 
 int check_common(const void *state, const SparcParams *p, int n_envs)
@@ -203,7 +219,8 @@ int check_common(const void *state, const SparcParams *p, int n_envs)
 }
 
 int launch_step(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
-                uint64_t seed, uint32_t env_id_base, const double *draws, void *stream)
+                uint64_t seed, uint32_t env_id_base, const double *draws, void *stream, float *tlog = nullptr,
+                int log_every = 0, int n_log_envs = 0)
 {
     int rc = check_common(state, p, n_envs);
     if (rc) return rc;
@@ -213,7 +230,7 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     if (n_us < 0) return fail(SPARC_E_INVALID, "n_us must be >= 0");
     if (n_us == 0) return SPARC_OK;
     const Variant *v = pick_variant(p->n_segments);
-    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large for the register-resident kernel");
+    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6145 wire segments)");
     sparc::StepArgs a;
     a.act = *actions;
     a.n_envs = n_envs;
@@ -221,10 +238,13 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     a.seed = seed;
     a.env_id_base = env_id_base;
     a.draws = draws;
+    a.tlog = tlog;
+    a.log_every = log_every;
+    a.n_log_envs = n_log_envs;
     SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
-    const int wpb = SPARC_BLOCK_THREADS / 32;   // one warp per environment
-    const int blocks = (n_envs + wpb - 1) / wpb;
-    v->fn[draws ? 1 : 0]<<<blocks, SPARC_BLOCK_THREADS, 0, (cudaStream_t)stream>>>(*p, S, a);
+    int blocks, threads;
+    launch_geometry(v, n_envs, &blocks, &threads);
+    v->fn[draws ? 1 : 0]<<<blocks, threads, 0, (cudaStream_t)stream>>>(*p, S, a);
     CUDA_TRY(cudaGetLastError());
     return SPARC_OK;
 }
@@ -291,6 +311,16 @@ int sparc_step_injected(void *state, const SparcParams *p, const SparcActions *a
 {
     if (!draws_dev) return fail(SPARC_E_INVALID, "null draws pointer");
     return launch_step(state, p, actions, n_envs, n_us, 0, 0, draws_dev, stream);
+}
+
+int sparc_step_logged(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+                      uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *tlog_dev, int log_every,
+                      int n_log_envs, void *stream)
+{
+    if (!tlog_dev) return fail(SPARC_E_INVALID, "null log pointer");
+    if (log_every <= 0 || n_log_envs < 0 || n_log_envs > n_envs) return fail(SPARC_E_INVALID, "bad log_every / n_log_envs");
+    return launch_step(state, p, actions, n_envs, n_us, seed, env_id_base, draws_dev, stream, tlog_dev, log_every,
+                       n_log_envs);
 }
 
 int sparc_observe(const void *state, int n_envs, int n_segments, float *obs_dev, void *stream)
@@ -388,12 +418,13 @@ int sparc_launch_info(int n_envs, int n_segments, int32_t out[4])
 {
     if (!out || n_envs <= 0 || n_segments < 2) return fail(SPARC_E_INVALID, "bad launch_info arguments");
     const Variant *v = pick_variant(n_segments);
-    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large for the register-resident kernel");
-    const int wpb = SPARC_BLOCK_THREADS / 32;
-    out[0] = 32;
+    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6145 wire segments)");
+    int blocks, threads;
+    launch_geometry(v, n_envs, &blocks, &threads);
+    out[0] = 32 * v->W;
     out[1] = v->K;
-    out[2] = SPARC_BLOCK_THREADS;
-    out[3] = (n_envs + wpb - 1) / wpb;
+    out[2] = threads;
+    out[3] = blocks;
     return SPARC_OK;
 }
 

@@ -87,6 +87,8 @@ struct StepArgs {
     uint64_t seed;
     uint32_t env_id_base;
     const double *draws;     // [n_envs][n_us][5] when INJECT
+    float *tlog;             // temperature-field log [n_log_envs][n_us / log_every][n_segments] or NULL
+    int log_every, n_log_envs;
 };
 
 #ifndef SPARC_BLOCK_THREADS

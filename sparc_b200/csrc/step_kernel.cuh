@@ -107,23 +107,59 @@ __device__ __forceinline__ float2 sub2(const float2 a, const float2 b)
     return __fadd2_rn(a, make_float2(-b.x, -b.y));
 }
 
+// ---- wires longer than one warp: W warps (one thread block) per environment -------------------
+// Each warp runs the scalar state machine redundantly (same inputs, same results, so control flow
+// is identical in all warps of the block); only three things cross warps: the stencil halos
+// (shared memory, double buffered, one barrier per µs), the temperature votes
+// (__syncthreads_or) and the zone-mean sum.
+template <int W>
+struct EnvCtx {
+    int lane, wid, gl;      // lane in warp, warp in env, lane in env
+    float (*halo)[W][2];    // [parity][warp][first, last]
+    int parity;
+};
+
+template <int W>
+__device__ __forceinline__ void stencil_halos(EnvCtx<W> &c, const float t_first, const float t_last, float &left,
+                                              float &right, const float spoolf)
+{
+    constexpr unsigned FULL = 0xffffffffu;
+    left = __shfl_up_sync(FULL, t_last, 1);
+    right = __shfl_down_sync(FULL, t_first, 1);
+    if constexpr (W > 1) {
+        float(*h)[2] = c.halo[c.parity];
+        if (c.lane == 0) h[c.wid][0] = t_first;
+        if (c.lane == 31) h[c.wid][1] = t_last;
+        __syncthreads();
+        if (c.lane == 0 && c.wid > 0) left = h[c.wid - 1][1];
+        if (c.lane == 31 && c.wid < W - 1) right = h[c.wid + 1][0];
+        c.parity ^= 1;
+    }
+    if (c.gl == 0) left = spoolf;
+}
+
+template <int W>
+__device__ __forceinline__ bool vote_any(const bool pred)
+{
+    if constexpr (W > 1) return __syncthreads_or(pred ? 1 : 0) != 0;
+    else return __any_sync(0xffffffffu, pred);
+}
+
 // n quiet µs of compute_thermal_update (wire.py:58-123) without heat sources.  HOT additionally
 // runs _check_wire_breaking (wire.py:376-388) every µs and returns the number of µs executed
 // (n, or j+1 when the wire broke on µs j; `broke` says which).
-template <int H, bool HOT>
+template <int H, bool HOT, int W>
 __device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], const float2 (&c0)[H],
-                                         const float2 (&cR)[H], const float ncL, const float spoolf, const int lane,
+                                         const float2 (&cR)[H], const float ncL, const float spoolf, EnvCtx<W> &ctx,
                                          const int n, const float crit_T, const float break_T, int &crit_count,
                                          bool &broke, bool &cold_after)
 {
-    constexpr unsigned FULL = 0xffffffffu;
     const float2 ncL2 = make_float2(ncL, ncL);
     broke = false;
 #pragma unroll 1
     for (int k = 0; k < n; k++) {
-        float left = __shfl_up_sync(FULL, T[H - 1].y, 1);
-        const float right = __shfl_down_sync(FULL, T[0].x, 1);
-        if (lane == 0) left = spoolf;
+        float left, right;
+        stencil_halos<W>(ctx, T[0].x, T[H - 1].y, left, right, spoolf);
         float2 dprev = sub2(T[0], make_float2(left, T[H - 1].x));
         const float2 last_next = make_float2(T[0].y, right);
         float lmax = spoolf;
@@ -138,10 +174,10 @@ __device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], 
             if (HOT) lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
         }
         if (HOT) {
-            const bool hot = __any_sync(FULL, lmax > crit_T);
+            const bool hot = vote_any<W>(lmax > crit_T);
             crit_count = hot ? crit_count + 1 : 0;
-            if (hot && __any_sync(FULL, lmax > break_T)) { broke = true; return k + 1; }
-            if (k == n - 1) cold_after = !__any_sync(FULL, lmax > crit_T - 1.0f);
+            if (hot && vote_any<W>(lmax > break_T)) { broke = true; return k + 1; }
+            if (k == n - 1) cold_after = !vote_any<W>(lmax > crit_T - 1.0f);
         }
     }
     if (!HOT) crit_count = 0;
@@ -156,24 +192,31 @@ constexpr int min_blocks_for(int K) { return K <= 13 ? SPARC_MINB_SMALL : (K <= 
 
 #define SPARC_LN2_UP 0.6931471805599460    /* ln2*(1+2^-50): u3 < fl(ln2/den) implies u3*den <= this */
 
-template <int K, bool INJECT>
-__global__ void __launch_bounds__(SPARC_BLOCK_THREADS, min_blocks_for(K))
+template <int K, bool INJECT, int W>
+__global__ void __launch_bounds__(W == 1 ? SPARC_BLOCK_THREADS : 32 * W, W == 1 ? min_blocks_for(K) : 1)
 step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
              const __grid_constant__ StepArgs a)
 {
     constexpr unsigned FULL = 0xffffffffu;
-    constexpr int WPB = SPARC_BLOCK_THREADS / 32;
-    __shared__ double sm_post[WPB][32];
+    // W == 1: one warp per env, SPARC_BLOCK_THREADS/32 envs per block; W > 1: one block of W warps per env
+    constexpr int WARPS = (W == 1) ? SPARC_BLOCK_THREADS / 32 : W;
+    __shared__ double sm_post[WARPS][32];
+    __shared__ float sm_halo[2][W][2];
+    __shared__ double sm_red[W];
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
-    const int e = blockIdx.x * WPB + wib;
-    if (e >= a.n_envs) return;                  // whole warp; no block-level barrier is used
+    const int e = (W == 1) ? blockIdx.x * WARPS + wib : blockIdx.x;
+    if (e >= a.n_envs) return;                  // whole env group (warp or block)
+    EnvCtx<W> ctx;
+    ctx.lane = lane; ctx.wid = (W == 1) ? 0 : wib; ctx.gl = ctx.wid * 32 + lane;
+    ctx.halo = sm_halo; ctx.parity = 0;
+    const int gl = ctx.gl;                      // lane within the env: owns slots gl*K .. gl*K+K-1
     double *post_s = sm_post[wib];
     const uint32_t k0 = (uint32_t)a.seed, k1 = (uint32_t)(a.seed >> 32);
 
     // ---------------- load ---------------------------------------------------------------------
     EnvState s;
-    s.e = e; s.it = 0; s.writer = lane == 0;
+    s.e = e; s.it = 0; s.writer = gl == 0;
     s.env_id = a.env_id_base + (uint32_t)e;
     s.episode = (uint32_t)S.episode[e];
     s.debris_density = S.debris_density[e]; s.flow = S.flow[e];
@@ -232,7 +275,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     float *Trow = S.T + (size_t)e * S.n_pad;
 #pragma unroll
     for (int j = 0; j < H; j++) {
-        const int sa = lane * K + j, sb = sa + H;
+        const int sa = gl * K + j, sb = sa + H;
         T[j].x = (sa < M) ? Trow[sa + 1] : spoolf;
         T[j].y = (sb < M) ? Trow[sb + 1] : spoolf;
     }
@@ -267,8 +310,8 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     auto refresh_coeffs = [&](float hb, float he) {
 #pragma unroll
         for (int j = 0; j < H; j++) {
-            slot_coeffs(lane * K + j, hb, he, cE[j].x, c0[j].x, cR[j].x);
-            slot_coeffs(lane * K + j + H, hb, he, cE[j].y, c0[j].y, cR[j].y);
+            slot_coeffs(gl * K + j, hb, he, cE[j].x, c0[j].x, cR[j].x);
+            slot_coeffs(gl * K + j + H, hb, he, cE[j].y, c0[j].y, cR[j].y);
         }
         const float hmax = fmaxf(hb, he), hmin = fminf(hb, he);
         const float ce_max = (float)(f * ((double)hmax * P.A));
@@ -279,9 +322,25 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     bool cold_ok = false;                       // max T < critical - 1 K after the last executed µs
 
     // contact span in slot coordinates of this lane
-    const int j_span_lo = P.contact_bottom_idx - 1 - lane * K;
-    const int j_span_hi = P.contact_top_idx - 1 - lane * K;
+    const int j_span_lo = P.contact_bottom_idx - 1 - gl * K;
+    const int j_span_hi = P.contact_top_idx - 1 - gl * K;
     const double *drow = INJECT ? a.draws + (size_t)e * a.n_us * SPARC_N_DRAW_SLOTS : nullptr;
+
+    // temperature-field logging (SimulationLogger "wire_temperature", utils/logger.py:128-150): row r
+    // holds the field after µs (r+1)*log_every - 1 of this call, layout (n_timesteps, n_segments)
+    const bool logging = a.tlog != nullptr && e < a.n_log_envs && a.log_every > 0;
+    const int log_rows = logging ? a.n_us / a.log_every : 0;
+    int it_term = 0;                            // launch-µs on which the env terminated
+    auto write_log_row = [&](int r) {
+        float *row = a.tlog + ((size_t)e * log_rows + r) * N;
+#pragma unroll
+        for (int j = 0; j < H; j++) {
+            const int sa = gl * K + j, sb = sa + H;
+            if (sa < M) row[sa + 1] = T[j].x;
+            if (sb < M) row[sb + 1] = T[j].y;
+        }
+        if (gl == 0) row[0] = spoolf;
+    };
 
     int it = 0;
     while (it < a.n_us && !done) {
@@ -366,6 +425,10 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 }
                 const unsigned stop = __ballot_sync(FULL, !ok) >> i;
                 n = stop ? __ffs(stop) - 1 : 32 - i;
+                if (logging) {                  // a run ends on the µs that is sampled
+                    const int room = a.log_every - (it + i) % a.log_every;
+                    if (n > room) n = room;
+                }
             }
             force_general = false;
 
@@ -374,9 +437,9 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 bool broke = false;
                 int nx;
                 if (cold_ok && convex)
-                    nx = run_quiet<H, false>(T, cE, c0, cR, ncL, spoolf, lane, n, 0.f, 0.f, crit_count, broke, cold_ok);
+                    nx = run_quiet<H, false, W>(T, cE, c0, cR, ncL, spoolf, ctx, n, 0.f, 0.f, crit_count, broke, cold_ok);
                 else
-                    nx = run_quiet<H, true>(T, cE, c0, cR, ncL, spoolf, lane, n, P.critical_temperature_f32,
+                    nx = run_quiet<H, true, W>(T, cE, c0, cR, ncL, spoolf, ctx, n, P.critical_temperature_f32,
                                             P.breaking_temperature_f32, crit_count, broke, cold_ok);
                 // scalar bookkeeping of the nx quiet µs (ignition.py:302-319, dielectric.py:104-144)
                 int n_idle = nx;
@@ -401,11 +464,14 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                     tsi_break = 0;
                     done = true;
                     time += nx - 1;
+                    it_term = it + i + nx - 1;
                     rewind_mech(i + nx - 1);
                     break;
                 }
                 time += nx;
                 i += nx;
+                if (logging && (it + i) % a.log_every == 0 && (it + i) / a.log_every <= log_rows)
+                    write_log_row((it + i) / a.log_every - 1);
                 continue;
             }
 
@@ -425,22 +491,21 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             if (s.refresh) refresh_coeffs(s.hb, s.he);
             if (s.freeze) {                     // crater-table miss: frozen before the thermal update
                 done = true;
-                rewind_mech(i);
+                it_term = it + i; rewind_mech(i);
                 break;
             }
             // ---- compute_thermal_update with sources (wire.py:58-123) -------------------------
             float lmax = spoolf;
             {
-                float left = __shfl_up_sync(FULL, T[H - 1].y, 1);
-                const float right = __shfl_down_sync(FULL, T[0].x, 1);
-                if (lane == 0) left = spoolf;
+                float left, right;
+                stencil_halos<W>(ctx, T[0].x, T[H - 1].y, left, right, spoolf);
                 float2 acc[H];
 #pragma unroll
                 for (int j = 0; j < H; j++) acc[j] = __ffma2_rn(cE[j], T[j], c0[j]);
                 if (s.heat_on) {
                     const float jA = s.jA, jB = s.jB, fP = s.fP;
                     const int jp = (s.spark_state == 1 && s.plasma_idx >= 0 && s.plasma_idx < N)
-                                       ? s.plasma_idx - 1 - lane * K : -(1 << 20);
+                                       ? s.plasma_idx - 1 - gl * K : -(1 << 20);
 #pragma unroll
                     for (int j = 0; j < H; j++) {
                         if (j >= j_span_lo && j <= j_span_hi) acc[j].x += fmaf(jA, T[j].x, jB);
@@ -463,11 +528,11 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 }
             }
             // ---- _check_wire_breaking (wire.py:376-388) ---------------------------------------
-            cold_ok = !__any_sync(FULL, lmax > P.critical_temperature_f32 - 1.0f);
+            cold_ok = !vote_any<W>(lmax > P.critical_temperature_f32 - 1.0f);
             bool hot = false, brk = false;
             if (!cold_ok) {
-                hot = __any_sync(FULL, lmax > P.critical_temperature_f32);
-                if (hot) brk = __any_sync(FULL, lmax > P.breaking_temperature_f32);
+                hot = vote_any<W>(lmax > P.critical_temperature_f32);
+                if (hot) brk = vote_any<W>(lmax > P.breaking_temperature_f32);
             }
             crit_count = hot ? crit_count + 1 : 0;
             // zone mean (wire.py:338-347, 390-394), only when enabled
@@ -479,13 +544,21 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                     float part = 0.0f;
 #pragma unroll
                     for (int jj = 0; jj < K; jj++) {     // ascending cell order within the lane
-                        int c = lane * K + jj + 1;
+                        int c = gl * K + jj + 1;
                         if (c >= za && c < zb) part += (jj < H) ? T[jj].x : T[jj - H].y;
                     }
-                    if (lane == 0 && za == 0) part += spoolf;    // cell 0 when the zone starts at 0
+                    if (gl == 0 && za == 0) part += spoolf;    // cell 0 when the zone starts at 0
                     double tot = (double)part;
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(FULL, tot, o);
+                    if constexpr (W > 1) {      // sum of the warps' partial sums, in warp order
+                        if (lane == 0) sm_red[ctx.wid] = tot;
+                        __syncthreads();
+                        tot = 0.0;
+#pragma unroll
+                        for (int w = 0; w < W; w++) tot += sm_red[w];
+                        __syncthreads();
+                    }
                     double zm = (double)(float)(tot / (double)(zb - za));
                     if (s.writer) { S.w_last_zone_mean[e] = zm; S.wire_avg_T[e] = zm; }
                     zone_mean_written = true;
@@ -497,7 +570,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
                 tsi_break = s.tsi_prev;
                 done = true;
-                rewind_mech(i);
+                it_term = it + i; rewind_mech(i);
                 break;
             }
             // mechanics of this µs is post_l of lane i; time bookkeeping (wire_edm.py:134-144)
@@ -507,20 +580,25 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             const double wire_after = __shfl_sync(FULL, post_l, i);
             if (wire_after > wp + 100.0) { flags |= SPARC_F_BROKEN; done = true; }
             else if (wp >= P.target_position) { flags |= SPARC_F_TARGET; done = true; }
-            if (done) { rewind_mech(i + 1); break; }
+            if (done) { it_term = it + i; rewind_mech(i + 1); break; }
             i += 1;
+            if (logging && (it + i) % a.log_every == 0 && (it + i) / a.log_every <= log_rows)
+                write_log_row((it + i) / a.log_every - 1);
         }
         it += nb;
+    }
+    if (logging && done) {                      // rows sampled at or after termination: the frozen field
+        for (int r = it_term / a.log_every; r < log_rows; r++) write_log_row(r);
     }
 
     // ---------------- store ------------------------------------------------------------------
 #pragma unroll
     for (int j = 0; j < H; j++) {
-        const int sa = lane * K + j, sb = sa + H;
+        const int sa = gl * K + j, sb = sa + H;
         if (sa < M) Trow[sa + 1] = T[j].x;
         if (sb < M) Trow[sb + 1] = T[j].y;
     }
-    if (lane == 0) {
+    if (gl == 0) {
         const bool thermal_break = (flags & SPARC_F_THERMAL_BREAK) != 0 && tsi_break >= 0;   // broke in THIS call
         const int win_steps = (time - time0) + (thermal_break ? 1 : 0);
         if (win_steps > 0 || (flags & SPARC_F_MODE_ERROR)) {

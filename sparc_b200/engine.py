@@ -124,6 +124,28 @@ class Engine:
                 N.check(self.lib.sparc_step_injected(self.blob.data_ptr(), C.byref(self.params), C.byref(a),
                                                      self.n_envs, int(n_us), draws.data_ptr(), self._stream()))
 
+    def step_logged(self, n_us: int, log_every: int, n_log_envs: Optional[int] = None,
+                    draws: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """step() that also samples the wire temperature field of envs [0, n_log_envs) every
+        `log_every` µs: returns [n_log_envs, n_us // log_every, n_segments] float32 (device), the
+        reference logger's (n_timesteps, n_segments) layout per env (utils/logger.py:128-150)."""
+        n_log = self.n_envs if n_log_envs is None else int(n_log_envs)
+        rows = int(n_us) // int(log_every)
+        a = self._actions_struct(self._act_dev)
+        with torch.cuda.device(self.device):
+            if out is None:
+                out = torch.zeros(n_log, rows, self.n_segments, dtype=torch.float32, device=self.device)
+            assert out.is_contiguous() and tuple(out.shape) == (n_log, rows, self.n_segments)
+            dptr = None
+            if draws is not None:
+                assert draws.dtype == torch.float64 and draws.is_contiguous() and draws.device == self.blob.device
+                assert tuple(draws.shape) == (self.n_envs, int(n_us), N.N_DRAW_SLOTS)
+                dptr = draws.data_ptr()
+            N.check(self.lib.sparc_step_logged(self.blob.data_ptr(), C.byref(self.params), C.byref(a), self.n_envs,
+                                               int(n_us), self.seed, self.env_id_base, dptr, out.data_ptr(),
+                                               int(log_every), n_log, self._stream()))
+        return out
+
     def step_host(self, n_us: int) -> torch.Tensor:
         """Host-buffer path: pinned host actions -> device, n_us steps, observation -> pinned host.
 

@@ -140,3 +140,41 @@ def test_on_device_philox_matches_oracle_philox(cfg_name, n_us):
     sparks = int(eng["stat_sparks"].sum().item())
     assert sparks > 0
     print(f"\n[{cfg_name}] philox mode: {sparks} sparks over {n_envs} envs, max |dT| {worst:.3e} K")
+
+
+@pytest.mark.parametrize("name,log_every", [("cfg2_default", 50), ("thick_2200", 100), ("thick_5500", 250),
+                                            ("hot_break", 200)])
+def test_logged_temperature_field_matches_oracle(name, log_every):
+    """BASELINE cfg 5: sparc_step_logged samples the whole wire temperature field every `log_every` µs
+    into the reference logger's (n_timesteps, n_segments) layout; compared with the oracle's
+    snapshots at the same µs (rows after a wire break hold the final field)."""
+    import torch
+
+    g = _golden(name)
+    case = CS.CASES[name]
+    actions = g["actions"]
+    n_us = min(case["n_us"], 4000) if name != "hot_break" else case["n_us"]
+    orc_env, tape, orc = PU.run_oracle_case(dict(case, n_us=n_us), actions, rec_every=1000, t_every=log_every)
+    eng = PU.make_engine(case, n_envs=3)
+    draws = torch.from_numpy(np.stack([tape[:n_us]] * 3)).to(eng.device)
+    rows_per_call = 1000 // log_every
+    worst, seen = 0.0, 0
+    T_ref_all = orc["T"]
+    for t0 in range(0, n_us, 1000):
+        n = min(1000, n_us - t0)
+        PU.stage_action(eng, PU.action_for_window(actions, t0, n))
+        log = eng.step_logged(n, log_every, n_log_envs=2, draws=draws[:, t0:t0 + n].contiguous())
+        assert tuple(log.shape) == (2, n // log_every, eng.n_segments)
+        L = log.cpu().numpy()
+        for r in range(L.shape[1]):
+            k = t0 // log_every + r
+            ref = T_ref_all[min(k, len(T_ref_all) - 1)]      # after termination the oracle stops sampling
+            for env_row in range(2):
+                err = np.abs(L[env_row, r].astype(np.float64) - ref.astype(np.float64))
+                worst = max(worst, float(err.max()))
+                assert np.all(err <= PU.T_ATOL + PU.T_RTOL * np.abs(ref)), f"{name} row {k}: max dT {err.max()}"
+            seen += 1
+        if int(eng["flags"][0].item()) & 2:
+            break
+    assert seen >= rows_per_call
+    print(f"\n[{name}] {seen} logged rows of {eng.n_segments} segments, max |dT| {worst:.3e} K")
