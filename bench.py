@@ -37,12 +37,17 @@ FLOP_PER_ENV_US = 13 * N_SEG + 60        # 13 flop/segment + ~60 sc
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--envs-per-gpu", type=int, default=4096)
     ap.add_argument("--impl", default="sparc_b200", choices=["sparc_b200", "reference"])
     ap.add_argument("--cpu-baseline-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--config", default="cfg2", choices=["cfg2", "cfg3", "cfg3_readme", "cfg5"],
+                    help="cfg2 (default, the metric's config) | cfg3 position mode + P gap controller, 16384 envs | "
+                         "cfg5 thick workpiece, fine segments, temperature-field logging")
+    ap.add_argument("--segment-len", type=float, default=0.05, help="cfg5: wire segment length [mm]")
+    ap.add_argument("--log-every", type=int, default=10, help="cfg5: sample the temperature field every N us")
     return ap.parse_args()
 
 
@@ -180,10 +185,50 @@ def run_gpu_arm(args):
 
     E = args.envs_per_gpu
     si = 1000
-    prm = P.derive_params(P.EnvironmentConfig(**README_CFG), "position")
-    assert prm.n_segments == N_SEG
+    workload, action, controller, log_every = WORKLOAD, ACTION, None, 0
+    if args.config == "cfg2":
+        prm = P.derive_params(P.EnvironmentConfig(**README_CFG), "position")
+        assert prm.n_segments == N_SEG
+    elif args.config in ("cfg3", "cfg3_readme"):
+        # BASELINE cfg 3: position mode, proportional gap controller evaluated on the device once per
+        # control step from wp - wire (README.md:82-99; stabilising sign of run_simulation.py:28-33)
+        if "--envs-per-gpu" not in " ".join(sys.argv):
+            E = 16384
+        prm = P.derive_params(P.EnvironmentConfig(**README_CFG), "position")
+        sign = 1.0 if args.config == "cfg3" else -1.0
+        workload = (f"cfg3: position mode, P gap controller servo = clip({'+' if sign > 0 else '-'}0.1*(gap-25), -1, 1) on "
+                    "device each control step, 80 V, I5, ON 3 / OFF 80, README default geometry, on-device Philox")
+
+        def controller(engine):
+            gap = engine["wp"] - engine["wire"]
+            servo = torch.clamp(sign * 0.1 * (gap - 25.0), -1.0, 1.0).to(torch.float32)
+            engine.set_actions(servo, 80.0, 5, 3.0, 80.0)
+    else:
+        # BASELINE cfg 5: 50 mm workpiece, fine segments, I13 ON 3 / OFF 30, full field logging
+        if "--envs-per-gpu" not in " ".join(sys.argv):
+            E = 1024
+        cfg5 = dict(workpiece_height=50.0, wire_diameter=0.25, wire_material="brass", target_cutting_distance=800.0)
+        prm = P.derive_params(P.EnvironmentConfig(**cfg5), "position",
+                              wire=P.WireModuleParameters(segment_len=args.segment_len))
+        action = (0.0, 80.0, 13, 3.0, 30.0)
+        log_every = args.log_every
+        workload = (f"cfg5: 50 mm workpiece, segment_len {args.segment_len} mm (N={prm.n_segments}), I13 ON 3 / OFF 30, "
+                    f"temperature field of every env logged every {log_every} us, on-device Philox")
+    n_seg = int(prm.n_segments)
+    flop_per_env_us = 13 * n_seg + 60
     eng = Engine(E, prm, device=dev, seed=20261104, env_id_base=rank * E)
-    eng.set_actions(*ACTION)
+    eng.set_actions(*action)
+    tlog = None
+    if log_every:
+        tlog = torch.zeros(E, si // log_every, n_seg, dtype=torch.float32, device=dev)
+
+    def one_step():
+        if controller is not None:
+            controller(eng)
+        if tlog is not None:
+            eng.step_logged(si, log_every, out=tlog)
+        else:
+            eng.step(si)
     stats = eng.stats_dev
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
@@ -196,7 +241,7 @@ def run_gpu_arm(args):
     sampler = ClockSampler(local_rank)
     sampler.start()                                 # samples cover warm-up + timed region (all under load)
     for _ in range(max(args.warmup, 3)):
-        eng.step(si)
+        one_step()
     barrier()
     K = args.steps
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
@@ -205,7 +250,7 @@ def run_gpu_arm(args):
     for k in range(K):
         flush.fill_(k & 0xFF)                       # evict the state from L2 (not timed)
         ev[k][0].record()
-        eng.step(si)
+        one_step()
         launches += 1
         if world > 1 and (k + 1) % 10 == 0:         # cfg 4: episode stats all-reduce every 10 control steps
             dist.all_reduce(eng.reduce_stats())
@@ -223,8 +268,8 @@ def run_gpu_arm(args):
 
     # ---- end-to-end arm: C-ABI call with host buffers (H2D actions, D2H observation) ----------
     ha = eng.host_actions
-    ha["servo"].fill_(ACTION[0]); ha["target_voltage"].fill_(ACTION[1]); ha["current_mode"].fill_(ACTION[2])
-    ha["on_time"].fill_(ACTION[3]); ha["off_time"].fill_(ACTION[4])
+    ha["servo"].fill_(action[0]); ha["target_voltage"].fill_(action[1]); ha["current_mode"].fill_(action[2])
+    ha["on_time"].fill_(action[3]); ha["off_time"].fill_(action[4])
     for _ in range(3):
         eng.step_host(si)
     barrier()
@@ -232,7 +277,7 @@ def run_gpu_arm(args):
     e0.record()
     obs_sum = 0.0
     for k in range(K):
-        ha["servo"].fill_(ACTION[0] + 1e-4 * (k % 3))       # host-side action of this step
+        ha["servo"].fill_(action[0] + 1e-4 * (k % 3))       # host-side action of this step
         obs = eng.step_host(si)                             # syncs; obs is pinned host memory
         obs_sum += float(obs[3].sum())
     e1.record()
@@ -256,17 +301,28 @@ def run_gpu_arm(args):
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+        traffic = None
+        try:    # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this launch
+            tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            key = f"{args.config}:{E}"
+            if key in tr:
+                traffic = tr[key]["dram_bytes_read"] + tr[key]["dram_bytes_write"]
+        except Exception:
+            pass
         kern_ms = sum(step_ms) / K
         bytes_per_launch = eng.bytes_per_control_step()
         ach_gbs = bytes_per_launch / (kern_ms * 1e-3) / 1e9
         per_gpu_rate = E * si / (kern_ms * 1e-3)
-        ach_tflops = per_gpu_rate * FLOP_PER_ENV_US / 1e12
+        ach_tflops = per_gpu_rate * flop_per_env_us / 1e12
+        if tlog is not None:
+            bytes_per_launch += tlog.numel() * 4
+            ach_gbs = bytes_per_launch / (kern_ms * 1e-3) / 1e9
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(args.warmup, 3),
             "ms_per_step": 1e3 * total_s / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64 scalars + f32 wire field", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "envs_per_gpu": E, "n_envs": world * E, "us_per_step": si,
-                       "n_segments": N_SEG, "l2": "flushed between timed steps (256 MiB fill)",
+            "config": {"workload": workload, "envs_per_gpu": E, "n_envs": world * E, "us_per_step": si,
+                       "n_segments": n_seg, "l2": "flushed between timed steps (256 MiB fill)",
                        "parallelism": f"env-sharded x{world}, NCCL all-reduce of fp64[8] stats every 10 steps",
                        "launch": eng.launch_info()},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 5 * 4 * E, "d2h_bytes_per_step": 8 * 4 * E,
@@ -274,13 +330,13 @@ def run_gpu_arm(args):
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": ach_gbs / hbm_peak, "traffic": None, "peak_source": hbm_src,
+                         "frac": ach_gbs / hbm_peak, "traffic": traffic, "peak_source": hbm_src,
                          "bytes_per_launch": bytes_per_launch,
                          "note": "state is read once and written once per 1000-us launch; the kernel is FP32-issue "
                                  "bound, not HBM bound (see roofline_fp32)"},
             "roofline_fp32": {"bound": "fp32_issue", "achieved": ach_tflops, "peak": fp32_peak, "unit": "TFLOP/s",
                               "frac": ach_tflops / fp32_peak if fp32_peak else None,
-                              "flop_per_env_us": FLOP_PER_ENV_US,
+                              "flop_per_env_us": flop_per_env_us,
                               "peak_source": "measured live: dense FFMA micro-kernel (sparc_measure_fp32_peak)"},
             "stats": {"sparks": ts[0], "short_us": ts[1], "env_us": ts[5], "broken": ts[6], "target_reached": ts[7],
                       "sparks_per_env_ms": ts[0] / max(ts[5], 1.0) * 1000.0},

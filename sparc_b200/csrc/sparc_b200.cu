@@ -12,7 +12,8 @@
 
 #include "../../include/sparc_b200.h"
 #include "state_layout.h"
-#include "step_kernel.cuh"
+#include "step_common.cuh"
+#include "step_variants.h"
 
 namespace {
 
@@ -168,32 +169,23 @@ __global__ void fma_peak_kernel(float *out, float a, float b, int iters)
 }
 
 // ---- step kernel dispatch -------------------------------------------------------------------
-using StepFn = void (*)(const SparcParams, const SparcStatePtrs, const sparc::StepArgs);
-
-struct Variant {
-    int K;           // cells per lane (even: the stencil is two-wide)
-    int W;           // warps per environment (1: warp per env, 4 envs per block; > 1: block per env)
-    StepFn fn[2];    // [INJECT]
-};
-
-#define VARIANT(K, W) {K, W, {sparc::step_kernel<K, false, W>, sparc::step_kernel<K, true, W>}}
-const Variant kVariants[] = {
-    VARIANT(4, 1),  VARIANT(8, 1),  VARIANT(12, 1), VARIANT(14, 1), VARIANT(16, 1), VARIANT(20, 1), VARIANT(24, 1),
-    VARIANT(16, 2), VARIANT(20, 2), VARIANT(24, 2),
-    VARIANT(16, 4), VARIANT(20, 4), VARIANT(24, 4),
-    VARIANT(16, 8), VARIANT(20, 8), VARIANT(24, 8),
-};
-constexpr int kNumVariants = (int)(sizeof(kVariants) / sizeof(kVariants[0]));
+using Variant = sparc::StepVariant;
 
 // fewest warps per env, then fewest cells per lane, whose 32*W*K slots hold the n_segments-1 dynamic cells
 const Variant *pick_variant(int n_segments)
 {
     const int M = n_segments - 1;
+    const Variant *(*tables[4])(int *) = {sparc::step_variants_w1, sparc::step_variants_w2, sparc::step_variants_w4,
+                                          sparc::step_variants_w8};
     const Variant *best = nullptr;
-    for (int i = 0; i < kNumVariants; i++) {
-        const Variant &v = kVariants[i];
-        if (v.K * 32 * v.W < M) continue;
-        if (!best || v.W < best->W || (v.W == best->W && v.K < best->K)) best = &v;
+    for (int t = 0; t < 4; t++) {
+        int n = 0;
+        const Variant *tab = tables[t](&n);
+        for (int i = 0; i < n; i++) {
+            const Variant &v = tab[i];
+            if (v.K * 32 * v.W < M) continue;
+            if (!best || v.W < best->W || (v.W == best->W && v.K < best->K)) best = &v;
+        }
     }
     return best;
 }
@@ -244,7 +236,7 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
     int blocks, threads;
     launch_geometry(v, n_envs, &blocks, &threads);
-    v->fn[draws ? 1 : 0]<<<blocks, threads, 0, (cudaStream_t)stream>>>(*p, S, a);
+    v->fn[tlog ? 1 : 0][draws ? 1 : 0]<<<blocks, threads, 0, (cudaStream_t)stream>>>(*p, S, a);
     CUDA_TRY(cudaGetLastError());
     return SPARC_OK;
 }

@@ -1,0 +1,14 @@
+// step_inst_w4.cu — step-kernel instantiations with 4 warp(s) per environment.
+#include "step_kernel.cuh"
+#include "step_variants.h"
+
+namespace sparc {
+static const StepVariant kTable[] = {
+    SPARC_STEP_VARIANT(16, 4), SPARC_STEP_VARIANT(20, 4), SPARC_STEP_VARIANT(24, 4),
+};
+const StepVariant *step_variants_w4(int *n)
+{
+    *n = (int)(sizeof(kTable) / sizeof(kTable[0]));
+    return kTable;
+}
+}  // namespace sparc

@@ -148,11 +148,11 @@ __device__ __forceinline__ bool vote_any(const bool pred)
 // n quiet µs of compute_thermal_update (wire.py:58-123) without heat sources.  HOT additionally
 // runs _check_wire_breaking (wire.py:376-388) every µs and returns the number of µs executed
 // (n, or j+1 when the wire broke on µs j; `broke` says which).
-template <int H, bool HOT, int W>
+template <int H, bool HOT, int W, bool LOG, class LogTick>
 __device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], const float2 (&c0)[H],
                                          const float2 (&cR)[H], const float ncL, const float spoolf, EnvCtx<W> &ctx,
                                          const int n, const float crit_T, const float break_T, int &crit_count,
-                                         bool &broke, bool &cold_after)
+                                         bool &broke, bool &cold_after, LogTick &&log_tick)
 {
     const float2 ncL2 = make_float2(ncL, ncL);
     broke = false;
@@ -173,6 +173,7 @@ __device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], 
             T[j] = __fadd2_rn(T[j], q);
             if (HOT) lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
         }
+        if (LOG) log_tick();
         if (HOT) {
             const bool hot = vote_any<W>(lmax > crit_T);
             crit_count = hot ? crit_count + 1 : 0;
@@ -192,7 +193,7 @@ constexpr int min_blocks_for(int K) { return K <= 13 ? SPARC_MINB_SMALL : (K <= 
 
 #define SPARC_LN2_UP 0.6931471805599460    /* ln2*(1+2^-50): u3 < fl(ln2/den) implies u3*den <= this */
 
-template <int K, bool INJECT, int W>
+template <int K, bool INJECT, int W, bool LOG>
 __global__ void __launch_bounds__(W == 1 ? SPARC_BLOCK_THREADS : 32 * W, W == 1 ? min_blocks_for(K) : 1)
 step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
              const __grid_constant__ StepArgs a)
@@ -203,6 +204,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     __shared__ double sm_post[WARPS][32];
     __shared__ float sm_halo[2][W][2];
     __shared__ double sm_red[W];
+    __shared__ float sm_log[LOG ? WARPS : 1][LOG ? 32 * (K + 1) : 1];   // field-log staging: coalesced row stores
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
     const int e = (W == 1) ? blockIdx.x * WARPS + wib : blockIdx.x;
@@ -328,18 +330,34 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
 
     // temperature-field logging (SimulationLogger "wire_temperature", utils/logger.py:128-150): row r
     // holds the field after µs (r+1)*log_every - 1 of this call, layout (n_timesteps, n_segments)
-    const bool logging = a.tlog != nullptr && e < a.n_log_envs && a.log_every > 0;
+    const bool logging = LOG && a.tlog != nullptr && e < a.n_log_envs && a.log_every > 0;
     const int log_rows = logging ? a.n_us / a.log_every : 0;
-    int it_term = 0;                            // launch-µs on which the env terminated
+    int log_ctr = logging ? a.log_every : 0;    // µs until the next sample
+    int log_row = 0;                            // next row to write
     auto write_log_row = [&](int r) {
         float *row = a.tlog + ((size_t)e * log_rows + r) * N;
+        float *stage = sm_log[wib];             // lane-major with an odd pitch: conflict-free both ways
 #pragma unroll
         for (int j = 0; j < H; j++) {
-            const int sa = gl * K + j, sb = sa + H;
-            if (sa < M) row[sa + 1] = T[j].x;
-            if (sb < M) row[sb + 1] = T[j].y;
+            stage[lane * (K + 1) + j] = T[j].x;
+            stage[lane * (K + 1) + j + H] = T[j].y;
         }
+        __syncwarp();
+        const int wbase = ctx.wid * 32 * K;     // first slot of this warp; slot s is cell s + 1
+#pragma unroll
+        for (int q = 0; q < K; q++) {
+            const int sl = q * 32 + lane;
+            if (wbase + sl < M) row[wbase + sl + 1] = stage[(sl / K) * (K + 1) + sl % K];
+        }
+        __syncwarp();
         if (gl == 0) row[0] = spoolf;
+    };
+    auto log_tick = [&]() {                     // called after every thermal update of a logged env
+        if (--log_ctr == 0) {
+            if (log_row < log_rows) write_log_row(log_row);
+            log_row += 1;
+            log_ctr = a.log_every;
+        }
     };
 
     int it = 0;
@@ -425,10 +443,6 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 }
                 const unsigned stop = __ballot_sync(FULL, !ok) >> i;
                 n = stop ? __ffs(stop) - 1 : 32 - i;
-                if (logging) {                  // a run ends on the µs that is sampled
-                    const int room = a.log_every - (it + i) % a.log_every;
-                    if (n > room) n = room;
-                }
             }
             force_general = false;
 
@@ -436,11 +450,22 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 // ================= quiet run ===================================================
                 bool broke = false;
                 int nx;
-                if (cold_ok && convex)
-                    nx = run_quiet<H, false, W>(T, cE, c0, cR, ncL, spoolf, ctx, n, 0.f, 0.f, crit_count, broke, cold_ok);
-                else
-                    nx = run_quiet<H, true, W>(T, cE, c0, cR, ncL, spoolf, ctx, n, P.critical_temperature_f32,
-                                            P.breaking_temperature_f32, crit_count, broke, cold_ok);
+                const bool cold = cold_ok && convex;
+                if (!LOG || !logging) {
+                    if (cold)
+                        nx = run_quiet<H, false, W, false>(T, cE, c0, cR, ncL, spoolf, ctx, n, 0.f, 0.f, crit_count, broke,
+                                                           cold_ok, log_tick);
+                    else
+                        nx = run_quiet<H, true, W, false>(T, cE, c0, cR, ncL, spoolf, ctx, n, P.critical_temperature_f32,
+                                                          P.breaking_temperature_f32, crit_count, broke, cold_ok, log_tick);
+                } else {
+                    if (cold)
+                        nx = run_quiet<H, false, W, LOG>(T, cE, c0, cR, ncL, spoolf, ctx, n, 0.f, 0.f, crit_count, broke,
+                                                         cold_ok, log_tick);
+                    else
+                        nx = run_quiet<H, true, W, LOG>(T, cE, c0, cR, ncL, spoolf, ctx, n, P.critical_temperature_f32,
+                                                        P.breaking_temperature_f32, crit_count, broke, cold_ok, log_tick);
+                }
                 // scalar bookkeeping of the nx quiet µs (ignition.py:302-319, dielectric.py:104-144)
                 int n_idle = nx;
                 if (spark_state == -2) {
@@ -464,14 +489,11 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                     tsi_break = 0;
                     done = true;
                     time += nx - 1;
-                    it_term = it + i + nx - 1;
                     rewind_mech(i + nx - 1);
                     break;
                 }
                 time += nx;
                 i += nx;
-                if (logging && (it + i) % a.log_every == 0 && (it + i) / a.log_every <= log_rows)
-                    write_log_row((it + i) / a.log_every - 1);
                 continue;
             }
 
@@ -491,7 +513,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             if (s.refresh) refresh_coeffs(s.hb, s.he);
             if (s.freeze) {                     // crater-table miss: frozen before the thermal update
                 done = true;
-                it_term = it + i; rewind_mech(i);
+                rewind_mech(i);
                 break;
             }
             // ---- compute_thermal_update with sources (wire.py:58-123) -------------------------
@@ -527,6 +549,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                     lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
                 }
             }
+            if (LOG && logging) log_tick();
             // ---- _check_wire_breaking (wire.py:376-388) ---------------------------------------
             cold_ok = !vote_any<W>(lmax > P.critical_temperature_f32 - 1.0f);
             bool hot = false, brk = false;
@@ -570,7 +593,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
                 tsi_break = s.tsi_prev;
                 done = true;
-                it_term = it + i; rewind_mech(i);
+                rewind_mech(i);
                 break;
             }
             // mechanics of this µs is post_l of lane i; time bookkeeping (wire_edm.py:134-144)
@@ -580,15 +603,13 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             const double wire_after = __shfl_sync(FULL, post_l, i);
             if (wire_after > wp + 100.0) { flags |= SPARC_F_BROKEN; done = true; }
             else if (wp >= P.target_position) { flags |= SPARC_F_TARGET; done = true; }
-            if (done) { it_term = it + i; rewind_mech(i + 1); break; }
+            if (done) { rewind_mech(i + 1); break; }
             i += 1;
-            if (logging && (it + i) % a.log_every == 0 && (it + i) / a.log_every <= log_rows)
-                write_log_row((it + i) / a.log_every - 1);
         }
         it += nb;
     }
-    if (logging && done) {                      // rows sampled at or after termination: the frozen field
-        for (int r = it_term / a.log_every; r < log_rows; r++) write_log_row(r);
+    if (LOG && logging && done) {               // rows sampled at or after termination: the frozen field
+        for (int r = log_row; r < log_rows; r++) write_log_row(r);
     }
 
     // ---------------- store ------------------------------------------------------------------
