@@ -92,7 +92,7 @@ struct StepArgs {
 };
 
 #ifndef SPARC_BLOCK_THREADS
-#define SPARC_BLOCK_THREADS 128
+#define SPARC_BLOCK_THREADS 64      /* W == 1: two envs per block; 7 blocks/SM = 14 warps/SM divides 4096 and 8192 envs into full waves */
 #endif
 
 // Sigmoid exponent above which the debris-short probability 1/(1+e^x) < 4.3e-18 can be treated

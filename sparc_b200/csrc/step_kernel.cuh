@@ -59,8 +59,7 @@ __device__ __forceinline__ void mech_step(const SparcParams &P, double &wire, do
 // the same operation sequence as mech_step without its branches).  Returns false if any clip
 // condition was met on any µs: the caller redoes the block with mech_step.
 __device__ __forceinline__ bool mech_block_noclip(const SparcParams &P, double &wire, double &v, double &prev_accel,
-                                                  const double target_delta, const int nb, double *post_s,
-                                                  const bool writer)
+                                                  const double target_delta, const int nb, double *post_s)
 {
     const double dt = P.mech_dt;
     bool bad = false;
@@ -76,7 +75,7 @@ __device__ __forceinline__ bool mech_block_noclip(const SparcParams &P, double &
             v += prev_accel * dt;
             bad = bad || !(fabs(v) <= P.max_speed);
             wire += v * dt;
-            if (writer) post_s[k] = wire;
+            post_s[k] = wire;                   // every lane stores the same value
         }
     } else {
         const double nw = -P.omega_n;
@@ -89,7 +88,7 @@ __device__ __forceinline__ bool mech_block_noclip(const SparcParams &P, double &
             v += prev_accel * dt;
             bad = bad || !(fabs(v) <= P.max_speed);
             wire += v * dt;
-            if (writer) post_s[k] = wire;
+            post_s[k] = wire;
         }
     }
     return !bad;
@@ -160,12 +159,14 @@ __device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], 
     for (int k = 0; k < n; k++) {
         float left, right;
         stencil_halos<W>(ctx, T[0].x, T[H - 1].y, left, right, spoolf);
-        float2 dprev = sub2(T[0], make_float2(left, T[H - 1].x));
-        const float2 last_next = make_float2(T[0].y, right);
+        // the three differences that cross a half boundary are scalar; the middle one is shared
+        const float d_mid = T[0].y - T[H - 1].x;
+        float2 dprev = make_float2(T[0].x - left, d_mid);
+        const float2 dlast = make_float2(d_mid, right - T[H - 1].y);
         float lmax = spoolf;
 #pragma unroll
         for (int j = 0; j < H; j++) {
-            const float2 dnext = sub2((j + 1 < H) ? T[j + 1] : last_next, T[j]);
+            const float2 dnext = (j + 1 < H) ? sub2(T[j + 1], T[j]) : dlast;
             float2 q = __ffma2_rn(cE[j], T[j], c0[j]);
             q = __ffma2_rn(cR[j], dnext, q);
             q = __ffma2_rn(ncL2, dprev, q);
@@ -187,9 +188,12 @@ __device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], 
 
 // resident blocks per SM the register budget is sized for
 #ifndef SPARC_MINB_SMALL
-#define SPARC_MINB_SMALL 4
+#define SPARC_MINB_SMALL 7
 #endif
-constexpr int min_blocks_for(int K) { return K <= 13 ? SPARC_MINB_SMALL : (K <= 20 ? 3 : 2); }
+constexpr int min_blocks_for(int K)
+{
+    return (K <= 13 ? SPARC_MINB_SMALL : (K <= 20 ? 6 : 4)) * 64 / SPARC_BLOCK_THREADS;
+}
 
 #define SPARC_LN2_UP 0.6931471805599460    /* ln2*(1+2^-50): u3 < fl(ln2/den) implies u3*den <= this */
 
@@ -377,7 +381,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         const double wire_b = wire;
         s.blk_wire = wire; s.blk_v = v; s.blk_pa = prev_accel;
         __syncwarp();
-        if (!mech_block_noclip(P, wire, v, prev_accel, delta_blk, nb, post_s, lane == 0)) {
+        if (!mech_block_noclip(P, wire, v, prev_accel, delta_blk, nb, post_s)) {
             wire = s.blk_wire; v = s.blk_v; prev_accel = s.blk_pa;     // a clip was active: exact path
 #pragma unroll 1
             for (int k = 0; k < nb; k++) {
@@ -537,11 +541,12 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                     }
                 }
                 const float2 ncL2 = make_float2(ncL, ncL);
-                float2 dprev = sub2(T[0], make_float2(left, T[H - 1].x));
-                const float2 last_next = make_float2(T[0].y, right);
+                const float d_mid = T[0].y - T[H - 1].x;
+                float2 dprev = make_float2(T[0].x - left, d_mid);
+                const float2 dlast = make_float2(d_mid, right - T[H - 1].y);
 #pragma unroll
                 for (int j = 0; j < H; j++) {
-                    const float2 dnext = sub2((j + 1 < H) ? T[j + 1] : last_next, T[j]);
+                    const float2 dnext = (j + 1 < H) ? sub2(T[j + 1], T[j]) : dlast;
                     float2 q = __ffma2_rn(cR[j], dnext, acc[j]);
                     q = __ffma2_rn(ncL2, dprev, q);
                     dprev = dnext;
