@@ -88,13 +88,18 @@ class BatchedWireEDMEnv:
         o = self.engine.observe()
         return {k: o[i] for i, k in enumerate(OBS_KEYS)}
 
-    def step(self, actions: Dict, n_us: Optional[int] = None, draws: Optional[torch.Tensor] = None):
+    def step(self, actions: Dict, n_us: Optional[int] = None, draws: Optional[torch.Tensor] = None,
+             log_temperature_every: Optional[int] = None, n_log_envs: Optional[int] = None):
         """Advance every env by `n_us` µs (default: one control step).  Returns the Gymnasium
         5-tuple with batched tensors: obs dict of [n_envs] float32, reward [n_envs] (0.0 — the
         reference's reward is a placeholder, wire_edm.py:185-187), terminated, truncated, info."""
         n_us = self.servo_interval if n_us is None else int(n_us)
         self._stage(actions)
-        self.engine.step(n_us, draws)
+        tlog = None
+        if log_temperature_every:
+            tlog = self.engine.step_logged(n_us, int(log_temperature_every), n_log_envs, draws)
+        else:
+            self.engine.step(n_us, draws)
         obs = self._obs()
         flags = self.engine["flags"]
         terminated = (flags & N.F_DONE) != 0
@@ -106,6 +111,8 @@ class BatchedWireEDMEnv:
             "time": self.engine["time"],
             "control_step": True,
         }
+        if tlog is not None:
+            info["wire_temperature_log"] = tlog     # [n_log_envs, n_us // every, n_segments]
         reward = torch.zeros(self.n_envs, dtype=torch.float32, device=self.device)
         truncated = torch.zeros(self.n_envs, dtype=torch.bool, device=self.device)
         if self.auto_reset:

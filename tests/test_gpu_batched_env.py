@@ -110,3 +110,32 @@ def test_statistics_match_running_reference():
     print(f"\nbreak: gpu P {broken.mean():.3f} mean t {steps.mean():.0f} us; ref P {r_broken.mean():.3f} mean t {r_steps.mean():.0f} us; z {z:+.2f}")
     assert abs(broken.mean() - r_broken.mean()) < 0.05
     assert abs(z) < 3.29
+
+
+def test_batched_logger_npz_layout(tmp_path):
+    """SimulationLogger equivalent: reference config dict and signal names; `.npz` arrays are
+    [n_samples, n_envs(, n_segments)]; kernel-sampled temperature rows at a sub-control-step interval."""
+    import numpy as np
+    from sparc_b200 import BatchedWireEDMEnv, EnvironmentConfig
+    from sparc_b200.utils.logger import SimulationLogger
+
+    cfg = EnvironmentConfig(workpiece_height=15.0, wire_diameter=0.25, target_cutting_distance=800.0)
+    venv = BatchedWireEDMEnv(8, config=cfg, seed=3)
+    venv.reset()
+    path = str(tmp_path / "log.npz")
+    logger = SimulationLogger({"signals_to_log": ["workpiece_position", "wire_position", "voltage", "is_short_circuit",
+                                                  "wire_temperature"],
+                               "log_frequency": {"type": "interval", "value": 250},
+                               "backend": {"type": "numpy", "filepath": path}}, env_reference=venv)
+    act = venv.constant_action(servo=0.1)
+    for _ in range(3):
+        _, _, _, _, info = venv.step(act, log_temperature_every=250)
+        logger.collect(info)
+    logger.finalize()
+    d = np.load(path)
+    assert d["wire_temperature"].shape == (12, 8, venv.n_segments)          # 3 steps x 4 rows
+    assert d["workpiece_position"].shape == (3, 8) and d["is_short_circuit"].dtype == np.bool_
+    np.testing.assert_array_equal(d["wire_temperature"][-1], venv.wire_temperature.cpu().numpy())
+    np.testing.assert_array_equal(d["wire_position"][-1], venv.state_tensor("wire").cpu().numpy())
+    with pytest.raises(ValueError):
+        SimulationLogger({"signals_to_log": [], "log_frequency": {"type": "control_step"}, "backend": {"type": "memory"}})
