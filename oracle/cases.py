@@ -104,6 +104,9 @@ CASES = {
                        mode="position", wire=dict(segment_len=0.02, compute_zone_mean=True, zone_mean_interval=250),
                        actions=[[0.0, 80.0, 13, 3.0, 30.0]], tape=("philox_forced", (32, (25, 500, 1200, 2600))),
                        n_us=3000),
+    # short servo interval: an action latch every 37 µs (look-ahead blocks are cut at every latch)
+    "short_servo": dict(config=dict(README_CFG, servo_interval=37, initial_gap=20.0), mode="position",
+                        actions=[[0.3, 90.0, 7, 2.0, 25.0]], tape=("philox", 77), n_us=6000),
     # deterministic KAT (i): single forced spark, no unwinding (single_spark_animation.py:214-249)
     "kat_single_spark": dict(config=README_CFG, mode="position", actions=[[0.0, 80.0, 5, 3.0, 80.0]],
                              tape=("never", (50,)), n_us=3000, unwind_v=0.0),
