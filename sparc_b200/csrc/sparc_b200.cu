@@ -49,22 +49,29 @@ const FieldDesc kFields[] = {
 #undef X
     {"episode", 'i', sizeof(int32_t)},
     {"T", 'f', sizeof(float)},
+    {"mech_traj", 'd', sizeof(double)},
+    {"mech_ckpt", 'd', sizeof(double)},
 };
 constexpr int kNumFields = (int)(sizeof(kFields) / sizeof(kFields[0]));
+constexpr int kFieldT = kNumFields - 3, kFieldTraj = kNumFields - 2, kFieldCkpt = kNumFields - 1;
 
 constexpr size_t kAlign = 256;
 
 int padded_segments(int n_segments) { return (int)sparc_align_up((size_t)n_segments, 32); }
 
+size_t field_count(int i, int n_envs, int n_segments)
+{
+    if (i == kFieldT) return (size_t)n_envs * padded_segments(n_segments);
+    if (i == kFieldTraj) return (size_t)n_envs * SPARC_MECH_EPOCH;
+    if (i == kFieldCkpt) return (size_t)n_envs * SPARC_MECH_NCKPT * 2;
+    return (size_t)n_envs;
+}
+
 // offset of field idx; idx == kNumFields gives total bytes
 size_t field_offset(int idx, int n_envs, int n_segments)
 {
     size_t off = 0;
-    for (int i = 0; i < idx; i++) {
-        size_t count = (size_t)n_envs;
-        if (i == kNumFields - 1) count = (size_t)n_envs * padded_segments(n_segments);
-        off = sparc_align_up(off + count * kFields[i].elem, kAlign);
-    }
+    for (int i = 0; i < idx; i++) off = sparc_align_up(off + field_count(i, n_envs, n_segments) * kFields[i].elem, kAlign);
     return off;
 }
 
@@ -78,6 +85,8 @@ SparcStatePtrs make_ptrs(void *state, int n_envs, int n_segments)
 #undef X
     S.episode = (int32_t *)(base + field_offset(idx++, n_envs, n_segments));
     S.T = (float *)(base + field_offset(idx++, n_envs, n_segments));
+    S.mech_traj = (double *)(base + field_offset(idx++, n_envs, n_segments));
+    S.mech_ckpt = (double *)(base + field_offset(idx++, n_envs, n_segments));
     S.n_pad = padded_segments(n_segments);
     return S;
 }
@@ -223,20 +232,26 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     if (n_us == 0) return SPARC_OK;
     const Variant *v = pick_variant(p->n_segments);
     if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6145 wire segments)");
-    sparc::StepArgs a;
-    a.act = *actions;
-    a.n_envs = n_envs;
-    a.n_us = n_us;
-    a.seed = seed;
-    a.env_id_base = env_id_base;
-    a.draws = draws;
-    a.tlog = tlog;
-    a.log_every = log_every;
-    a.n_log_envs = n_log_envs;
     SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
     int blocks, threads;
     launch_geometry(v, n_envs, &blocks, &threads);
-    v->fn[tlog ? 1 : 0][draws ? 1 : 0]<<<blocks, threads, 0, (cudaStream_t)stream>>>(*p, S, a);
+    // one (mechanics pre-pass, fused step) pair per epoch of SPARC_MECH_EPOCH µs
+    for (int ep0 = 0; ep0 < n_us; ep0 += SPARC_MECH_EPOCH) {
+        sparc::StepArgs a;
+        a.act = *actions;
+        a.n_envs = n_envs;
+        a.n_us = (n_us - ep0 < SPARC_MECH_EPOCH) ? n_us - ep0 : SPARC_MECH_EPOCH;
+        a.seed = seed;
+        a.env_id_base = env_id_base;
+        a.draws = draws;
+        a.tlog = tlog;
+        a.log_every = log_every;
+        a.n_log_envs = n_log_envs;
+        a.it_base = ep0;
+        a.total_us = n_us;
+        sparc::mech_launch(*p, S, a, (cudaStream_t)stream);
+        v->fn[tlog ? 1 : 0][draws ? 1 : 0]<<<blocks, threads, 0, (cudaStream_t)stream>>>(*p, S, a);
+    }
     CUDA_TRY(cudaGetLastError());
     return SPARC_OK;
 }
@@ -258,7 +273,7 @@ int sparc_field_info(int idx, int n_envs, int n_segments, const char **name, cha
     if (name) *name = kFields[idx].name;
     if (dtype) *dtype = kFields[idx].dtype;
     if (byte_offset) *byte_offset = field_offset(idx, n_envs, n_segments);
-    if (count) *count = (idx == kNumFields - 1) ? (size_t)n_envs * padded_segments(n_segments) : (size_t)n_envs;
+    if (count) *count = field_count(idx, n_envs, n_segments);
     return SPARC_OK;
 }
 

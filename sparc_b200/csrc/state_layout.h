@@ -70,6 +70,13 @@
     X(win_short_us, int32_t, 'i', 0)                                                              \
     X(win_steps, int32_t, 'i', 0)
 
+// Mechanics look-ahead scratch (written by mech_kernel, read by the step kernel in the same call;
+// carries nothing between calls): wire position after each µs of a launch epoch, and
+// (velocity, prev_accel) checkpoints every SPARC_MECH_CKPT µs plus the end-of-epoch pair.
+#define SPARC_MECH_EPOCH 1024
+#define SPARC_MECH_CKPT 32
+#define SPARC_MECH_NCKPT (SPARC_MECH_EPOCH / SPARC_MECH_CKPT + 1)
+
 // `episode` is the only field that survives a reset (it is incremented instead).
 struct SparcStatePtrs {
 #define X(name, ctype, dt, init) ctype *name;
@@ -77,6 +84,8 @@ struct SparcStatePtrs {
 #undef X
     int32_t *episode;
     float *T;       // [n_envs][n_pad]
+    double *mech_traj;   // [n_envs][SPARC_MECH_EPOCH]
+    double *mech_ckpt;   // [n_envs][SPARC_MECH_NCKPT][2]
     int32_t n_pad;
 };
 

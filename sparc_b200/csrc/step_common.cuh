@@ -87,8 +87,9 @@ struct StepArgs {
     uint64_t seed;
     uint32_t env_id_base;
     const double *draws;     // [n_envs][n_us][5] when INJECT
-    float *tlog;             // temperature-field log [n_log_envs][n_us / log_every][n_segments] or NULL
+    float *tlog;             // temperature-field log [n_log_envs][total_us / log_every][n_segments] or NULL
     int log_every, n_log_envs;
+    int it_base, total_us;   // this launch covers µs [it_base, it_base + n_us) of a call of total_us µs
 };
 
 #ifndef SPARC_BLOCK_THREADS
@@ -130,8 +131,6 @@ struct EnvState {
     int e, it;
     uint32_t env_id, episode;
     bool writer;
-    // ---- mechanics state at the start of the current look-ahead block (step_kernel2.cuh) ----
-    double blk_wire, blk_v, blk_pa;
 };
 
 // generator settings as the ignition module sees them (ignition.py:329-343, 98-113): `x or
@@ -217,7 +216,7 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
     const int e = s.e;
     const uint32_t k0 = (uint32_t)a.seed, k1 = (uint32_t)(a.seed >> 32);
     auto draw = [&](int slot) -> double {
-        if (INJECT) return a.draws[((size_t)e * a.n_us + s.it) * SPARC_N_DRAW_SLOTS + slot];
+        if (INJECT) return a.draws[((size_t)e * a.total_us + a.it_base + s.it) * SPARC_N_DRAW_SLOTS + slot];
         uint32_t w[4];
         philox4x32_10(s.env_id, (uint32_t)s.time >> 2, s.episode, (uint32_t)slot, k0, k1, w);
         return u01(pick4(w, s.time & 3));
@@ -411,5 +410,36 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
     }
     prepare_fast(s, P);
 }
+
+// MechanicsModule.update (mechanics.py:79-114), one µs.
+__device__ __forceinline__ void mech_step(const SparcParams &P, double &wire, double &v, double &prev_accel,
+                                          const double target_delta)
+{
+    double a_nom;
+    if (P.control_mode == 0) {
+        double x_err = wire - (wire + target_delta);
+        a_nom = P.damping_coeff * v + P.stiffness_coeff * x_err;
+    } else {
+        a_nom = -P.omega_n * (v - target_delta);
+    }
+    double da = a_nom - prev_accel;
+    if (fabs(a_nom) <= P.max_acceleration && fabs(da) <= P.max_jerk_dt) {
+        prev_accel = prev_accel + da;           // no clip active
+    } else {
+        if (a_nom > P.max_acceleration) a_nom = P.max_acceleration;
+        else if (a_nom < -P.max_acceleration) a_nom = -P.max_acceleration;
+        da = a_nom - prev_accel;
+        if (da > P.max_jerk_dt) da = P.max_jerk_dt;
+        else if (da < -P.max_jerk_dt) da = -P.max_jerk_dt;
+        prev_accel = prev_accel + da;
+    }
+    v += prev_accel * P.mech_dt;
+    if (!(fabs(v) <= P.max_speed)) {
+        if (v > P.max_speed) v = P.max_speed;
+        else if (v < -P.max_speed) v = -P.max_speed;
+    }
+    wire += v * P.mech_dt;
+}
+
 
 }  // namespace sparc

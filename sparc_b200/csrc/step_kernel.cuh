@@ -25,75 +25,6 @@
 
 namespace sparc {
 
-// MechanicsModule.update (mechanics.py:79-114), one µs.
-__device__ __forceinline__ void mech_step(const SparcParams &P, double &wire, double &v, double &prev_accel,
-                                          const double target_delta)
-{
-    double a_nom;
-    if (P.control_mode == 0) {
-        double x_err = wire - (wire + target_delta);
-        a_nom = P.damping_coeff * v + P.stiffness_coeff * x_err;
-    } else {
-        a_nom = -P.omega_n * (v - target_delta);
-    }
-    double da = a_nom - prev_accel;
-    if (fabs(a_nom) <= P.max_acceleration && fabs(da) <= P.max_jerk_dt) {
-        prev_accel = prev_accel + da;           // no clip active
-    } else {
-        if (a_nom > P.max_acceleration) a_nom = P.max_acceleration;
-        else if (a_nom < -P.max_acceleration) a_nom = -P.max_acceleration;
-        da = a_nom - prev_accel;
-        if (da > P.max_jerk_dt) da = P.max_jerk_dt;
-        else if (da < -P.max_jerk_dt) da = -P.max_jerk_dt;
-        prev_accel = prev_accel + da;
-    }
-    v += prev_accel * P.mech_dt;
-    if (!(fabs(v) <= P.max_speed)) {
-        if (v > P.max_speed) v = P.max_speed;
-        else if (v < -P.max_speed) v = -P.max_speed;
-    }
-    wire += v * P.mech_dt;
-}
-
-// nb µs of mechanics assuming no acceleration / jerk / speed clip is active (then the update is
-// the same operation sequence as mech_step without its branches).  Returns false if any clip
-// condition was met on any µs: the caller redoes the block with mech_step.
-__device__ __forceinline__ bool mech_block_noclip(const SparcParams &P, double &wire, double &v, double &prev_accel,
-                                                  const double target_delta, const int nb, double *post_s)
-{
-    const double dt = P.mech_dt;
-    bool bad = false;
-    if (P.control_mode == 0) {
-        const double c1 = P.damping_coeff, c2 = P.stiffness_coeff;
-#pragma unroll 4
-        for (int k = 0; k < nb; k++) {
-            const double x_err = wire - (wire + target_delta);
-            const double a_nom = c1 * v + c2 * x_err;
-            const double da = a_nom - prev_accel;
-            bad = bad || !(fabs(a_nom) <= P.max_acceleration) || !(fabs(da) <= P.max_jerk_dt);
-            prev_accel = prev_accel + da;
-            v += prev_accel * dt;
-            bad = bad || !(fabs(v) <= P.max_speed);
-            wire += v * dt;
-            post_s[k] = wire;                   // every lane stores the same value
-        }
-    } else {
-        const double nw = -P.omega_n;
-#pragma unroll 4
-        for (int k = 0; k < nb; k++) {
-            const double a_nom = nw * (v - target_delta);
-            const double da = a_nom - prev_accel;
-            bad = bad || !(fabs(a_nom) <= P.max_acceleration) || !(fabs(da) <= P.max_jerk_dt);
-            prev_accel = prev_accel + da;
-            v += prev_accel * dt;
-            bad = bad || !(fabs(v) <= P.max_speed);
-            wire += v * dt;
-            post_s[k] = wire;
-        }
-    }
-    return !bad;
-}
-
 // ---- packed stencil ---------------------------------------------------------------------------
 // sm_100 has two-wide fp32 instructions (FFMA2/FADD2, PTX fma.rn.f32x2): one issue slot and one
 // pipe pass for two IEEE-rn operations — measured 1.95 FFMA2 vs 2.1 register-operand FFMA per
@@ -205,7 +136,6 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     constexpr unsigned FULL = 0xffffffffu;
     // W == 1: one warp per env, SPARC_BLOCK_THREADS/32 envs per block; W > 1: one block of W warps per env
     constexpr int WARPS = (W == 1) ? SPARC_BLOCK_THREADS / 32 : W;
-    __shared__ double sm_post[WARPS][32];
     __shared__ float sm_halo[2][W][2];
     __shared__ double sm_red[W];
     __shared__ float sm_log[LOG ? WARPS : 1][LOG ? 32 * (K + 1) : 1];   // field-log staging: coalesced row stores
@@ -217,7 +147,6 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     ctx.lane = lane; ctx.wid = (W == 1) ? 0 : wib; ctx.gl = ctx.wid * 32 + lane;
     ctx.halo = sm_halo; ctx.parity = 0;
     const int gl = ctx.gl;                      // lane within the env: owns slots gl*K .. gl*K+K-1
-    double *post_s = sm_post[wib];
     const uint32_t k0 = (uint32_t)a.seed, k1 = (uint32_t)(a.seed >> 32);
 
     // ---------------- load ---------------------------------------------------------------------
@@ -330,14 +259,14 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     // contact span in slot coordinates of this lane
     const int j_span_lo = P.contact_bottom_idx - 1 - gl * K;
     const int j_span_hi = P.contact_top_idx - 1 - gl * K;
-    const double *drow = INJECT ? a.draws + (size_t)e * a.n_us * SPARC_N_DRAW_SLOTS : nullptr;
+    const double *drow = INJECT ? a.draws + ((size_t)e * a.total_us + a.it_base) * SPARC_N_DRAW_SLOTS : nullptr;
 
     // temperature-field logging (SimulationLogger "wire_temperature", utils/logger.py:128-150): row r
     // holds the field after µs (r+1)*log_every - 1 of this call, layout (n_timesteps, n_segments)
     const bool logging = LOG && a.tlog != nullptr && e < a.n_log_envs && a.log_every > 0;
-    const int log_rows = logging ? a.n_us / a.log_every : 0;
-    int log_ctr = logging ? a.log_every : 0;    // µs until the next sample
-    int log_row = 0;                            // next row to write
+    const int log_rows = logging ? a.total_us / a.log_every : 0;
+    int log_ctr = logging ? a.log_every - a.it_base % a.log_every : 0;  // µs until the next sample
+    int log_row = logging ? a.it_base / a.log_every : 0;                // next row to write
     auto write_log_row = [&](int r) {
         float *row = a.tlog + ((size_t)e * log_rows + r) * N;
         float *stage = sm_log[wib];             // lane-major with an odd pitch: conflict-free both ways
@@ -364,35 +293,27 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         }
     };
 
+    // mechanics pre-pass results of this launch (mech_kernel)
+    const double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
+    const double wire0 = wire, delta_old0 = target_delta, delta_new0 = (double)a.act.servo[e];
+    const int first_latch_it = (next_latch - time > 0) ? next_latch - time : 0;
+
     int it = 0;
     while (it < a.n_us && !done) {
-        // ================= block setup: mechanics look-ahead ==================================
+        // ================= block setup ==========================================================
         int nb = a.n_us - it;
         if (nb > 32) nb = 32;
         int to_latch = next_latch - time;
-        double delta_blk = target_delta;
         bool force_general = false;
         if (to_latch <= 0) {                    // the first µs of this block latches the action
-            delta_blk = (double)a.act.servo[e];
             to_latch = (P.servo_interval > 1) ? P.servo_interval : 1;
             force_general = true;
         }
         if (nb > to_latch) nb = to_latch;       // a block never straddles a latch
-        const double wire_b = wire;
-        s.blk_wire = wire; s.blk_v = v; s.blk_pa = prev_accel;
-        __syncwarp();
-        if (!mech_block_noclip(P, wire, v, prev_accel, delta_blk, nb, post_s)) {
-            wire = s.blk_wire; v = s.blk_v; prev_accel = s.blk_pa;     // a clip was active: exact path
-#pragma unroll 1
-            for (int k = 0; k < nb; k++) {
-                mech_step(P, wire, v, prev_accel, delta_blk);
-                if (lane == 0) post_s[k] = wire;
-            }
-        }
-        __syncwarp();
-        const double post_l = post_s[(lane < nb) ? lane : nb - 1];      // wire after µs `lane`
+        // wire positions of this block from the mechanics pre-pass: lane l holds µs it + l
+        const double post_l = traj[it + ((lane < nb) ? lane : nb - 1)];  // wire after µs `lane`
         double pre_l = __shfl_up_sync(FULL, post_l, 1);                  // wire before µs `lane`
-        if (lane == 0) pre_l = wire_b;
+        if (lane == 0) pre_l = (it == 0) ? wire0 : traj[it - 1];
         // ignition roll of µs `lane` (slot 2): word (time+lane)&3 of Philox block (time+lane)>>2
         uint32_t w_l = 0;
         if (!INJECT) {
@@ -401,11 +322,17 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             philox4x32_10(s.env_id, tl >> 2, s.episode, 2u, k0, k1, w);
             w_l = pick4(w, tl & 3);
         }
-        // finished inside this block: exact mechanics state after `steps` µs of it
+        // finished inside this block: exact mechanics state after `steps` µs of it, replayed from
+        // the pre-pass checkpoint (same operation sequence as mech_kernel)
         auto rewind_mech = [&](int steps) {
-            wire = s.blk_wire; v = s.blk_v; prev_accel = s.blk_pa;
+            const int target = it + steps;
+            const int c = target / SPARC_MECH_CKPT;
+            const double *ck = S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + c) * 2;
+            wire = (c == 0) ? wire0 : traj[c * SPARC_MECH_CKPT - 1];
+            v = ck[0]; prev_accel = ck[1];
 #pragma unroll 1
-            for (int k = 0; k < steps; k++) mech_step(P, wire, v, prev_accel, delta_blk);
+            for (int k = c * SPARC_MECH_CKPT; k < target; k++)
+                mech_step(P, wire, v, prev_accel, (k >= first_latch_it) ? delta_new0 : delta_old0);
         };
 
         int i = 0;
@@ -612,6 +539,11 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             i += 1;
         }
         it += nb;
+    }
+    if (!done) {                                // end-of-launch mechanics state from the pre-pass
+        wire = traj[a.n_us - 1];
+        v = S.mech_ckpt[((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2];
+        prev_accel = S.mech_ckpt[((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2 + 1];
     }
     if (LOG && logging && done) {               // rows sampled at or after termination: the frozen field
         for (int r = log_row; r < log_rows; r++) write_log_row(r);

@@ -3,6 +3,7 @@
 #pragma once
 #include "../../include/sparc_b200.h"
 #include "state_layout.h"
+#include <cuda_runtime.h>
 
 namespace sparc {
 struct StepArgs;
@@ -13,6 +14,9 @@ struct StepVariant {
     int W;              // warps per environment (1: warp per env, several envs per block; > 1: block per env)
     StepFn fn[2][2];    // [LOG][INJECT]
 };
+
+// mechanics pre-pass of one launch epoch (mech_kernel.cu)
+void mech_launch(const SparcParams &P, const SparcStatePtrs &S, const StepArgs &a, cudaStream_t stream);
 
 const StepVariant *step_variants_w1(int *n);
 const StepVariant *step_variants_w2(int *n);

@@ -179,7 +179,8 @@ class Engine:
 
     def bytes_per_control_step(self) -> int:
         """Algorithmic HBM bytes one step call moves: the whole state read once and written once."""
-        return 2 * int(self.blob.numel())
+        scratch = sum(int(self.fields[k].numel()) * 8 for k in ("mech_traj", "mech_ckpt") if k in self.fields)
+        return 2 * (int(self.blob.numel()) - scratch)
 
 
 def measure_fp32_peak(device="cuda:0") -> float:

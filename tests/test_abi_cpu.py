@@ -39,9 +39,13 @@ def test_params_struct_size_matches_c(native):
     tab = native.field_table(1000, 375)
     offs = [t[2] for t in tab]
     assert offs == sorted(offs) and all(o % 256 == 0 for o in offs)
+    by_name = {t[0]: t for t in tab}
+    name, dt, off, cnt = by_name["T"]
+    assert dt == "f" and cnt == 1000 * native.lib().sparc_padded_segments(375)
+    # mechanics pre-pass scratch: wire trajectory of one 1024-µs epoch + (v, prev_accel) checkpoints
+    assert by_name["mech_traj"][3] == 1000 * 1024 and by_name["mech_ckpt"][3] == 1000 * 33 * 2
     name, dt, off, cnt = tab[-1]
-    assert name == "T" and dt == "f" and cnt == 1000 * native.lib().sparc_padded_segments(375)
-    assert native.lib().sparc_state_bytes(1000, 375) >= off + cnt * 4
+    assert native.lib().sparc_state_bytes(1000, 375) >= off + cnt * 8
     assert C.sizeof(SparcParams) % 8 == 0
 
 

@@ -178,3 +178,32 @@ def test_logged_temperature_field_matches_oracle(name, log_every):
             break
     assert seen >= rows_per_call
     print(f"\n[{name}] {seen} logged rows of {eng.n_segments} segments, max |dT| {worst:.3e} K")
+
+
+def test_long_launch_equals_split_launches():
+    """A 2500-µs call (three mechanics epochs of <= 1024 µs inside the library) gives bit-identical
+    state and log rows to 1000 + 1000 + 500 µs calls, with injected draws and with on-device Philox."""
+    import torch
+    from sparc_b200.engine import Engine
+
+    case = CS.CASES["short_servo"]
+    prm = PU.case_params(case)
+    tape = CS.case_tape(case)[:2500]
+    skip = {"win_vsum", "win_sparks", "win_short_us", "win_steps", "mech_traj", "mech_ckpt"}
+    for injected in (True, False):
+        engs = [Engine(4, prm, seed=11, env_id_base=5) for _ in range(2)]
+        draws = torch.from_numpy(np.stack([tape] * 4)).to(engs[0].device) if injected else None
+        for eng in engs:
+            PU.stage_action(eng, case["actions"][0])
+        log_a = engs[0].step_logged(2500, 100, draws=draws)
+        parts, t0 = [], 0
+        for n in (1000, 1000, 500):
+            d = draws[:, t0:t0 + n].contiguous() if injected else None
+            parts.append(engs[1].step_logged(n, 100, draws=d))
+            t0 += n
+        log_b = torch.cat(parts, dim=1)
+        assert torch.equal(log_a, log_b)
+        for name, t in engs[0].fields.items():
+            if name not in skip:
+                assert torch.equal(t, engs[1].fields[name]), name
+        assert int(engs[0]["time"][0].item()) == 2500
