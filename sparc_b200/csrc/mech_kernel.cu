@@ -11,6 +11,39 @@ namespace sparc {
 // issue cycles each on B200 and were 27 % of the fused kernel when every warp ran them for its own
 // env).  Output: the wire position after every µs (read back 32 µs at a time, one per lane) and
 // (velocity, prev_accel) checkpoints for the rare exact rewind when an env terminates.
+// One block of <= SPARC_MECH_CKPT µs without clip handling: the same operation sequence as mech_step
+// when no acceleration / jerk / speed clip is active; the clip tests only accumulate a flag (off
+// the dependency chain, which is what bounds this latency-bound kernel).  Returns false if any
+// clip condition was met: the caller redoes the block with mech_step.
+template <int MODE>
+__device__ __forceinline__ bool mech_block_fast(const SparcParams &P, double &wire, double &v, double &pa, const int it0,
+                                                const int nb, const int first_latch, const double d_old,
+                                                const double d_new, double *traj)
+{
+    const double dt = P.mech_dt, c1 = P.damping_coeff, c2 = P.stiffness_coeff, nw = -P.omega_n;
+    const double amax = P.max_acceleration, jmax = P.max_jerk_dt, vmax = P.max_speed;
+    bool bad = false;
+#pragma unroll 4
+    for (int k = 0; k < nb; k++) {
+        const double delta = (it0 + k >= first_latch) ? d_new : d_old;
+        double a_nom;
+        if (MODE == 0) {
+            const double x_err = wire - (wire + delta);
+            a_nom = c1 * v + c2 * x_err;
+        } else {
+            a_nom = nw * (v - delta);
+        }
+        const double da = a_nom - pa;
+        bad = bad || !(fabs(a_nom) <= amax) || !(fabs(da) <= jmax);
+        pa = pa + da;
+        v += pa * dt;
+        bad = bad || !(fabs(v) <= vmax);
+        wire += v * dt;
+        traj[it0 + k] = wire;
+    }
+    return !bad;
+}
+
 __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ SparcParams P,
                                                    const __grid_constant__ SparcStatePtrs S,
                                                    const __grid_constant__ StepArgs a)
@@ -19,19 +52,30 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
     if (e >= a.n_envs) return;
     if (S.flags[e] & SPARC_F_DONE) return;
     double wire = S.wire[e], v = S.v[e], pa = S.prev_accel[e];
-    double delta = S.target_delta[e];
-    const double delta_new = (double)a.act.servo[e];
-    const int period = (P.servo_interval > 1) ? P.servo_interval : 1;
-    int latch = P.servo_interval - S.t_servo[e];        // launch-µs of the next action latch (wire_edm.py:117)
-    if (latch < 0) latch = 0;
+    const double d_old = S.target_delta[e];
+    const double d_new = (double)a.act.servo[e];
+    // launch-µs of the next action latch (wire_edm.py:117); later latches re-latch the same command
+    int first_latch = P.servo_interval - S.t_servo[e];
+    if (first_latch < 0) first_latch = 0;
     double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
     double *ck = S.mech_ckpt + (size_t)e * SPARC_MECH_NCKPT * 2;
 #pragma unroll 1
-    for (int it = 0; it < a.n_us; it++) {
-        if (it % SPARC_MECH_CKPT == 0) { ck[2 * (it / SPARC_MECH_CKPT)] = v; ck[2 * (it / SPARC_MECH_CKPT) + 1] = pa; }
-        if (it == latch) { delta = delta_new; latch += period; }
-        mech_step(P, wire, v, pa, delta);
-        traj[it] = wire;
+    for (int it0 = 0; it0 < a.n_us; it0 += SPARC_MECH_CKPT) {
+        const int nb = (a.n_us - it0 < SPARC_MECH_CKPT) ? a.n_us - it0 : SPARC_MECH_CKPT;
+        ck[2 * (it0 / SPARC_MECH_CKPT)] = v;
+        ck[2 * (it0 / SPARC_MECH_CKPT) + 1] = pa;
+        const double w0 = wire, v0 = v, p0 = pa;
+        const bool ok = (P.control_mode == 0)
+                            ? mech_block_fast<0>(P, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj)
+                            : mech_block_fast<1>(P, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj);
+        if (!ok) {                              // a clip was active somewhere in the block: exact path
+            wire = w0; v = v0; pa = p0;
+#pragma unroll 1
+            for (int k = 0; k < nb; k++) {
+                mech_step(P, wire, v, pa, (it0 + k >= first_latch) ? d_new : d_old);
+                traj[it0 + k] = wire;
+            }
+        }
     }
     ck[2 * (SPARC_MECH_NCKPT - 1)] = v;                 // end-of-launch pair
     ck[2 * (SPARC_MECH_NCKPT - 1) + 1] = pa;
@@ -39,7 +83,7 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
 
 void mech_launch(const SparcParams &P, const SparcStatePtrs &S, const StepArgs &a, cudaStream_t stream)
 {
-    mech_kernel<<<(a.n_envs + 127) / 128, 128, 0, stream>>>(P, S, a);
+    mech_kernel<<<(a.n_envs + 31) / 32, 32, 0, stream>>>(P, S, a);   // latency-bound: one warp per SM
 }
 
 }  // namespace sparc
