@@ -168,6 +168,10 @@ int sparc_reduce_stats(const void *state, int n_envs, int n_segments, double *ou
  * (pinned for full speed); `scratch_dev` is caller-owned device scratch of
  * sparc_host_scratch_bytes(n_envs) bytes. */
 size_t sparc_host_scratch_bytes(int n_envs);
+/* If the five host action arrays lie in ONE host buffer, array k at byte offset
+ * k * sparc_host_action_pitch(n_envs) (order: servo, target_voltage, current_mode, on_time,
+ * off_time), sparc_step_host moves them with a single copy instead of five. */
+size_t sparc_host_action_pitch(int n_envs);
 int sparc_step_host(void *state, const SparcParams *p, const SparcActions *actions_host, int n_envs,
                     int n_us, uint64_t seed, uint32_t env_id_base, void *scratch_dev,
                     float *obs_host, void *stream);

@@ -32,7 +32,7 @@ _lib = None
 EXPORTS = ("sparc_abi_version", "sparc_last_error", "sparc_num_fields", "sparc_field_info",
            "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_step",
            "sparc_step_injected", "sparc_step_logged", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
-           "sparc_step_host", "sparc_launch_info", "sparc_measure_fp32_peak")
+           "sparc_step_host", "sparc_host_action_pitch", "sparc_launch_info", "sparc_measure_fp32_peak")
 
 
 def lib():
@@ -63,6 +63,8 @@ def lib():
     L.sparc_reduce_stats.argtypes = [vp, i32, i32, vp, vp]
     L.sparc_host_scratch_bytes.restype = sz
     L.sparc_host_scratch_bytes.argtypes = [i32]
+    L.sparc_host_action_pitch.restype = sz
+    L.sparc_host_action_pitch.argtypes = [i32]
     L.sparc_step_host.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, vp]
     L.sparc_measure_fp32_peak.argtypes = [vp, sz, C.POINTER(C.c_double)]
     L.sparc_launch_info.argtypes = [i32, i32, C.POINTER(C.c_int32)]

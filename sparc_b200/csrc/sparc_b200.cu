@@ -354,6 +354,12 @@ int sparc_reduce_stats(const void *state, int n_envs, int n_segments, double *ou
     return SPARC_OK;
 }
 
+size_t sparc_host_action_pitch(int n_envs)
+{
+    if (n_envs <= 0) return 0;
+    return sparc_align_up((size_t)n_envs * 4, kAlign);
+}
+
 size_t sparc_host_scratch_bytes(int n_envs)
 {
     if (n_envs <= 0) return 0;
@@ -378,11 +384,18 @@ int sparc_step_host(void *state, const SparcParams *p, const SparcActions *ah, i
     ad.off_time = (const float *)(d + 4 * n);
     float *obs_dev = (float *)(d + 5 * n);
     size_t bytes = (size_t)n_envs * 4;
-    CUDA_TRY(cudaMemcpyAsync((void *)ad.servo, ah->servo, bytes, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync((void *)ad.target_voltage, ah->target_voltage, bytes, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync((void *)ad.current_mode, ah->current_mode, bytes, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync((void *)ad.on_time, ah->on_time, bytes, cudaMemcpyHostToDevice, st));
-    CUDA_TRY(cudaMemcpyAsync((void *)ad.off_time, ah->off_time, bytes, cudaMemcpyHostToDevice, st));
+    const char *h0 = (const char *)ah->servo;
+    if ((const char *)ah->target_voltage == h0 + n && (const char *)ah->current_mode == h0 + 2 * n &&
+        (const char *)ah->on_time == h0 + 3 * n && (const char *)ah->off_time == h0 + 4 * n) {
+        // the five host arrays sit in one buffer with the scratch pitch (sparc_host_action_pitch): one copy
+        CUDA_TRY(cudaMemcpyAsync(d, h0, 4 * n + bytes, cudaMemcpyHostToDevice, st));
+    } else {
+        CUDA_TRY(cudaMemcpyAsync((void *)ad.servo, ah->servo, bytes, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync((void *)ad.target_voltage, ah->target_voltage, bytes, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync((void *)ad.current_mode, ah->current_mode, bytes, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync((void *)ad.on_time, ah->on_time, bytes, cudaMemcpyHostToDevice, st));
+        CUDA_TRY(cudaMemcpyAsync((void *)ad.off_time, ah->off_time, bytes, cudaMemcpyHostToDevice, st));
+    }
     rc = launch_step(state, p, &ad, n_envs, n_us, seed, env_id_base, nullptr, stream);
     if (rc) return rc;
     rc = sparc_observe(state, n_envs, p->n_segments, obs_dev, stream);

@@ -60,7 +60,11 @@ class Engine:
             self.stats_dev = torch.zeros(N.N_STATS, dtype=torch.float64, device=self.device)
             self._scratch = torch.zeros(self.lib.sparc_host_scratch_bytes(self.n_envs), dtype=torch.uint8,
                                         device=self.device)
-            self._act_host = {k: torch.zeros(self.n_envs, dtype=v.dtype).pin_memory() for k, v in self._act_dev.items()}
+            # one pinned buffer, five arrays at the library's pitch: sparc_step_host moves them in one copy
+            pitch = int(self.lib.sparc_host_action_pitch(self.n_envs))
+            self._act_host_buf = torch.zeros(5 * pitch, dtype=torch.uint8).pin_memory()
+            self._act_host = {k: self._act_host_buf[i * pitch: i * pitch + 4 * self.n_envs].view(v.dtype)
+                              for i, (k, v) in enumerate(self._act_dev.items())}
             self.obs_host = torch.zeros(N.N_OBS, self.n_envs, dtype=torch.float32).pin_memory()
             N.check(self.lib.sparc_init(self.blob.data_ptr(), C.byref(self.params), self.n_envs, self._stream()))
 
