@@ -267,18 +267,43 @@ def run_gpu_arm(args):
     value = world * E * si * K / total_s
 
     # ---- end-to-end arm: C-ABI call with host buffers (H2D actions, D2H observation) ----------
+    # Same workload as the device arm: cfg3 evaluates the gap controller on the HOST from the returned
+    # observation (the way a reference user would); cfg5 also brings the logged field to pinned host
+    # memory (through a <= 1 GiB pinned staging buffer, every byte crosses PCIe).
     ha = eng.host_actions
     ha["servo"].fill_(action[0]); ha["target_voltage"].fill_(action[1]); ha["current_mode"].fill_(action[2])
     ha["on_time"].fill_(action[3]); ha["off_time"].fill_(action[4])
-    for _ in range(3):
-        eng.step_host(si)
+    d2h_extra = 0
+    stage = None
+    if tlog is not None:
+        flat = tlog.view(-1)
+        chunk = min(flat.numel(), (1 << 30) // 4)
+        stage = torch.empty(chunk, dtype=torch.float32, pin_memory=True)
+        d2h_extra = flat.numel() * 4
+
+    def e2e_step(k, obs_prev):
+        if controller is not None and obs_prev is not None:
+            torch.clamp(sign * 0.1 * (obs_prev[0] - 25.0), -1.0, 1.0, out=ha["servo"])
+        else:
+            ha["servo"].fill_(action[0] + 1e-4 * (k % 3))   # host-side action of this step
+        if tlog is None:
+            return eng.step_host(si)                        # syncs; obs is pinned host memory
+        eng.set_actions(ha["servo"], ha["target_voltage"], ha["current_mode"], ha["on_time"], ha["off_time"])
+        eng.step_logged(si, log_every, out=tlog)
+        for o in range(0, flat.numel(), chunk):
+            n = min(chunk, flat.numel() - o)
+            stage[:n].copy_(flat[o:o + n], non_blocking=True)
+        return eng.observe().cpu()                          # syncs
+
+    obs = None
+    for k in range(3):
+        obs = e2e_step(k, obs)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     obs_sum = 0.0
     for k in range(K):
-        ha["servo"].fill_(action[0] + 1e-4 * (k % 3))       # host-side action of this step
-        obs = eng.step_host(si)                             # syncs; obs is pinned host memory
+        obs = e2e_step(k, obs)
         obs_sum += float(obs[3].sum())
     e1.record()
     barrier()
@@ -325,8 +350,9 @@ def run_gpu_arm(args):
                        "n_segments": n_seg, "l2": "flushed between timed steps (256 MiB fill)",
                        "parallelism": f"env-sharded x{world}, NCCL all-reduce of fp64[8] stats every 10 steps",
                        "launch": eng.launch_info()},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 5 * 4 * E, "d2h_bytes_per_step": 8 * 4 * E,
-                    "api": "sparc_step_host (C-ABI, pinned host action/observation buffers)"},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 5 * 4 * E, "d2h_bytes_per_step": 8 * 4 * E + d2h_extra,
+                    "api": ("sparc_step_host (C-ABI, pinned host action/observation buffers)" if tlog is None else
+                            "sparc_step_logged + D2H of the logged field to pinned host memory")},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",

@@ -16,10 +16,14 @@ __version__ = "0.1.0"
 
 def __getattr__(name):
     # envs/engine import torch; keep `import sparc_b200` light
-    if name in ("WireEDMEnv", "BatchedWireEDMEnv"):
+    if name in ("WireEDMEnv", "BatchedWireEDMEnv", "WireEDMVectorEnv"):
         from . import envs
 
         return getattr(envs, name)
+    if name in ("GapController", "VoltageController"):
+        from . import controllers
+
+        return getattr(controllers, name)
     if name == "Engine":
         from .engine import Engine
 
@@ -29,7 +33,8 @@ def __getattr__(name):
 
 __all__ = [
     "EDMState", "DeviceStateView", "crater_dtype", "EnvironmentConfig", "MaterialDatabase", "WireMaterial",
-    "get_material_db", "WireEDMEnv", "BatchedWireEDMEnv", "Engine", "EDMModule",
+    "get_material_db", "WireEDMEnv", "BatchedWireEDMEnv", "WireEDMVectorEnv", "GapController",
+    "VoltageController", "Engine", "EDMModule",
     "IgnitionModule", "IgnitionModuleParameters", "WireModule", "WireModuleParameters",
     "MaterialRemovalModule", "MaterialModuleParameters", "DielectricModule", "DielectricModuleParameters",
     "MechanicsModule", "MechanicsModuleParameters", "derive_params",

@@ -1,4 +1,5 @@
 from .batched import BatchedWireEDMEnv  # noqa: F401
+from .vector import WireEDMVectorEnv  # noqa: F401
 from .wire_edm import WireEDMEnv  # noqa: F401
 
-__all__ = ["WireEDMEnv", "BatchedWireEDMEnv"]
+__all__ = ["WireEDMEnv", "BatchedWireEDMEnv", "WireEDMVectorEnv"]

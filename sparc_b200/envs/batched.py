@@ -121,6 +121,14 @@ class BatchedWireEDMEnv:
             self._arm_latch(terminated)
         return obs, reward, terminated, truncated, info
 
+    def mean_voltage(self) -> torch.Tensor:
+        """float64 [n_envs]: mean gap voltage over the µs of the last step call (the 1 ms voltage
+        history the reference's PI controller averages, run_simulation.py:68-72); the instantaneous
+        voltage when nothing has been stepped yet."""
+        steps = self.engine["win_steps"]
+        return torch.where(steps > 0, self.engine["win_vsum"] / steps.clamp(min=1).to(torch.float64),
+                           self.engine["voltage"])
+
     def step_host(self, n_us: Optional[int] = None) -> torch.Tensor:
         """Host-buffer control step through `sparc_step_host`: fill `self.engine.host_actions`
         (pinned) first; returns the pinned [8, n_envs] observation array."""

@@ -1,0 +1,156 @@
+"""SURVEY §8(f) rank 2 on the GPU: on-device controllers in closed loop against the oracle driven by
+the reference's controller arithmetic, and the Gymnasium VectorEnv-shaped adapter (auto-reset
+modes, truncation, rewards)."""
+import numpy as np
+import pytest
+
+import parity_util as PU
+from oracle import cases as CS
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+README = dict(workpiece_height=15.0, wire_diameter=0.25, wire_material="brass", target_cutting_distance=800.0)
+
+
+def _tape(n_envs, n_us, key):
+    g = np.random.Generator(np.random.Philox(key=key))
+    u = g.random((n_envs, n_us, 4))
+    z = g.standard_normal((n_envs, n_us, 1))
+    return np.ascontiguousarray(np.concatenate([u, z], axis=2))
+
+
+@pytest.mark.parametrize("mode", ["position", "velocity"])
+def test_gap_controller_closed_loop_matches_oracle(mode):
+    """BASELINE cfg 3: the batched GapController closes the loop on the device; the oracle is driven
+    by the reference's controller arithmetic (run_simulation.py:27-39) evaluated in numpy from its
+    own state each control step.  Same injected draws => same trajectories, discrete fields exact."""
+    import torch
+    from sparc_b200 import BatchedWireEDMEnv, EnvironmentConfig, GapController
+
+    E, STEPS, SI = 6, 12, 1000
+    gen = dict(target_voltage=80.0, current_mode=5, ON_time=3.0, OFF_time=80.0)
+    if mode == "position":
+        ctrl = GapController(25.0, "position", limit=1.0, generator=gen)        # cfg 3 settings
+        ref_servo = lambda gap: np.float32(np.clip((gap - 25.0) * 0.1, -1.0, 1.0))
+    else:
+        ctrl = GapController(25.0, "velocity", generator=gen)                   # reference gains
+        ref_servo = lambda gap: np.float32(np.clip((gap - 25.0) * 50.0, -1000.0, 1000.0))
+    tape = _tape(E, STEPS * SI, key=777)
+    env = BatchedWireEDMEnv(E, config=EnvironmentConfig(**README), mechanics_control_mode=mode,
+                            latch_first_action=False)
+    env.reset()
+    case = {"config": README, "mode": mode}
+    oracles = [O.OracleEnv(**CS.oracle_overrides(case)) for _ in range(E)]
+    tape_dev = torch.from_numpy(tape).cuda()
+    for k in range(STEPS):
+        env.step(ctrl(env), draws=tape_dev[:, k * SI:(k + 1) * SI].contiguous())
+        f_ref, i_ref = [], []
+        for e, orc in enumerate(oracles):
+            f, _ = orc.record()
+            servo = ref_servo(f[0] - f[1])
+            orc.run(SI, [[float(servo), 80.0, 5, 3.0, 80.0]], draws=tape[e, k * SI:(k + 1) * SI], rec_every=0)
+            f, i = orc.record()
+            f_ref.append(f)
+            i_ref.append(i)
+        f_gpu, i_gpu = PU.read_rows(env.engine, range(E))
+        PU.assert_rows_match(f_gpu, i_gpu, np.stack(f_ref), np.stack(i_ref).astype(np.int64),
+                             where=f"{mode} control step {k}")
+    assert float(env.state_tensor("stat_sparks").sum()) > 0
+
+
+def test_voltage_controller_closed_loop():
+    """PI voltage controller: the integral state and the command follow the reference's update
+    (run_simulation.py:74-98) restated in numpy on the mean voltages the env reports."""
+    import torch
+    from sparc_b200 import BatchedWireEDMEnv, EnvironmentConfig, VoltageController
+
+    E = 256
+    env = BatchedWireEDMEnv(E, config=EnvironmentConfig(**README), seed=3)
+    env.reset()
+    ctrl = VoltageController(30.0, "position")
+    integ = np.zeros(E)
+    for k in range(15):
+        mv = env.mean_voltage().cpu().numpy()
+        act = ctrl(env)
+        err = 30.0 - mv
+        integ = np.clip(integ + err, -100.0, 100.0)
+        want = np.clip(-(0.05 * err + 0.1 * integ * 0.001), -5.0, 5.0).astype(np.float32)
+        np.testing.assert_array_equal(act["servo"].cpu().numpy(), want)
+        np.testing.assert_array_equal(ctrl.integral.cpu().numpy(), integ)
+        obs, *_ = env.step(act)
+        # the observation's mean_voltage is the float32 view of the same average
+        np.testing.assert_allclose(obs["mean_voltage"].cpu().numpy(), env.mean_voltage().cpu().numpy(), rtol=1e-6)
+    assert torch.all(env.state_tensor("time") == 15000)
+    mv = env.mean_voltage()
+    assert float(mv.min()) >= 0.0 and float(mv.max()) <= 80.0 + 1e-9
+    ctrl.reset(torch.arange(E, device=env.device) < 10)
+    assert float(ctrl.integral[:10].abs().sum()) == 0.0
+
+
+def _short_episode_env(n, **kw):
+    from sparc_b200 import EnvironmentConfig, WireEDMVectorEnv
+
+    cfg = dict(README, target_cutting_distance=50.0005)      # the first spark reaches the target
+    return WireEDMVectorEnv(n, config=EnvironmentConfig(**cfg), seed=9, **kw)
+
+
+def test_vector_env_spaces_and_next_step_autoreset():
+    n = 128
+    venv = _short_episode_env(n, reward="progress")
+    assert venv.num_envs == n and venv.metadata["autoreset_mode"] == "next_step"
+    assert venv.single_observation_space.shape == (7,) and venv.observation_space.shape == (n, 7)
+    assert set(venv.single_action_space.spaces) == {"servo", "generator_control"}
+    obs, info = venv.reset(seed=9)
+    assert isinstance(obs, np.ndarray) and obs.shape == (n, 7) and obs.dtype == np.float32 and info == {}
+    assert np.all(obs[:, 0] == 50.0)
+    act = venv.action_space.sample()
+    act["servo"][:] = 0.05
+    act["generator_control"]["current_mode"][:] = 5
+    act["generator_control"]["target_voltage"][:] = 80.0
+    act["generator_control"]["ON_time"][:] = 3.0
+    act["generator_control"]["OFF_time"][:] = 80.0
+    prev_term = np.zeros(n, dtype=bool)
+    seen_term = 0
+    for k in range(12):
+        obs, rew, term, trunc, info = venv.step(act)
+        assert obs.shape == (n, 7) and rew.shape == (n,) and term.dtype == bool and not trunc.any()
+        # an env that was terminal in the previous call comes back reset: gap 50, time 0, reward 0
+        if prev_term.any():
+            assert not term[prev_term].any()
+            assert np.all(obs[prev_term, 0] == 50.0) and np.all(info["time"][prev_term] == 0)
+            assert np.all(rew[prev_term] == 0.0)
+        assert np.all(info["target_reached"] == term)        # the only way to end in this config
+        assert np.all(rew[term] > 0.0)                        # the spark's workpiece advance
+        seen_term += int(term.sum())
+        prev_term = term.copy()
+    assert seen_term > n // 4
+
+
+def test_vector_env_same_step_truncation_and_disabled():
+    import torch
+
+    n = 64
+    venv = _short_episode_env(n, autoreset_mode="same_step", max_episode_steps=3, to_numpy=False)
+    obs, _ = venv.reset()
+    assert isinstance(obs, torch.Tensor) and obs.is_cuda
+    act = {"servo": 0.0, "generator_control": {"target_voltage": 80.0, "current_mode": 5, "ON_time": 3.0, "OFF_time": 80.0}}
+    ends = 0
+    for k in range(9):
+        obs, rew, term, trunc, info = venv.step(act)
+        done = term | trunc
+        assert not (term & trunc).any()
+        if done.any():
+            assert torch.all(obs[done, 0] == 50.0)                       # reset observation
+            assert torch.equal(info["_final_obs"], done)
+            assert torch.all(info["time"][term] > 0)                       # info describes the final state
+            ends += int(done.sum())
+        assert torch.all(rew == 0.0)                                       # reference placeholder reward
+    assert ends >= n * 2                                                   # every env ends at least every 3 steps
+    ven2 = _short_episode_env(8, autoreset_mode="disabled")
+    ven2.reset()
+    for _ in range(10):
+        obs, rew, term, trunc, info = ven2.step(act)
+    assert term.all() and np.all(info["time"] < 10000)                    # frozen once terminal, never reset
+    with pytest.raises(ValueError):
+        _short_episode_env(4, autoreset_mode="sometimes")
