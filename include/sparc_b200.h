@@ -38,6 +38,27 @@ extern "C" {
 #define SPARC_N_STATS 8
 #define SPARC_N_OBS 8
 
+/* rows of the per-signal log (sparc_step_sampled); names are the reference's EDMState attributes */
+enum {
+    SPARC_SIG_TIME = 0,              /* time */
+    SPARC_SIG_VOLTAGE = 1,           /* voltage */
+    SPARC_SIG_CURRENT = 2,           /* current */
+    SPARC_SIG_WIRE_POSITION = 3,     /* wire_position */
+    SPARC_SIG_WIRE_VELOCITY = 4,     /* wire_velocity */
+    SPARC_SIG_WORKPIECE_POSITION = 5,/* workpiece_position */
+    SPARC_SIG_TARGET_DELTA = 6,      /* target_delta */
+    SPARC_SIG_DEBRIS_DENSITY = 7,    /* debris_density (= legacy debris_concentration, dielectric.py:159-163) */
+    SPARC_SIG_FLOW_RATE = 8,         /* flow_rate (= legacy dielectric_flow_rate) */
+    SPARC_SIG_IS_SHORT_CIRCUIT = 9,  /* is_short_circuit */
+    SPARC_SIG_SPARK_STATE = 10,      /* spark_status[0] */
+    SPARC_SIG_MAX_TEMPERATURE = 11,  /* max(wire_temperature) */
+    SPARC_SIG_AVERAGE_TEMPERATURE = 12, /* wire_average_temperature */
+    SPARC_SIG_DEBRIS_VOLUME = 13,    /* debris_volume */
+    SPARC_SIG_TIME_IN_CRITICAL = 14, /* time_in_critical_temp */
+    SPARC_SIG_FLAGS = 15,            /* SPARC_F_* bits */
+    SPARC_N_SIGNALS = 16
+};
+
 enum {
     SPARC_OK = 0,
     SPARC_E_INVALID = -1,   /* bad argument (NULL pointer, negative size, unsupported geometry) */
@@ -153,6 +174,17 @@ int sparc_step_injected(void *state, const SparcParams *p, const SparcActions *a
 int sparc_step_logged(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
                       uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *tlog_dev, int log_every,
                       int n_log_envs, void *stream);
+
+/* Step with per-signal logging: the device-side SimulationLogger (utils/logger.py:105-160,
+ * "every_step" with sample_every = 1, "interval" with sample_every = value).  After every
+ * `sample_every` µs of this call one row of the scalar signals above is written:
+ * signals_dev[n_us / sample_every][SPARC_N_SIGNALS][n_envs] doubles, row r = the state after µs
+ * (r+1)*sample_every - 1, i.e. what the reference's logger reads from EDMState after that step().
+ * The call is cut into launches at the sampling µs (results are independent of the cut).  draws_dev
+ * and tlog_dev / log_every / n_log_envs as in sparc_step_logged, both optional (NULL). */
+int sparc_step_sampled(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+                       uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *tlog_dev, int log_every,
+                       int n_log_envs, double *signals_dev, int sample_every, void *stream);
 
 /* Observation summary of the last step call, obs_dev[SPARC_N_OBS][n_envs] float32:
  * 0 gap [µm], 1 wire_velocity [µm/s], 2 mean voltage over the call [V], 3 sparks ignited in the

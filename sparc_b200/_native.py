@@ -12,6 +12,11 @@ LIB_PATH = os.environ.get("SPARC_LIB_PATH") or os.path.join(HERE, "_lib", "libsp
 N_OBS = 8
 N_STATS = 8
 N_DRAW_SLOTS = 5
+# rows of the per-signal log (include/sparc_b200.h SPARC_SIG_*), by the reference's EDMState names
+SIGNALS = ("time", "voltage", "current", "wire_position", "wire_velocity", "workpiece_position", "target_delta",
+           "debris_density", "flow_rate", "is_short_circuit", "spark_state", "max_wire_temperature",
+           "wire_average_temperature", "debris_volume", "time_in_critical_temp", "flags")
+N_SIGNALS = len(SIGNALS)
 
 F_SHORT, F_BROKEN, F_TARGET, F_MODE_ERROR, F_HAS_Y, F_THERMAL_BREAK = 1, 2, 4, 8, 16, 32
 F_DONE = F_BROKEN | F_TARGET | F_MODE_ERROR
@@ -31,7 +36,7 @@ _lib = None
 # every symbol include/sparc_b200.h declares
 EXPORTS = ("sparc_abi_version", "sparc_last_error", "sparc_num_fields", "sparc_field_info",
            "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_step",
-           "sparc_step_injected", "sparc_step_logged", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
+           "sparc_step_injected", "sparc_step_logged", "sparc_step_sampled", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
            "sparc_step_host", "sparc_host_action_pitch", "sparc_launch_info", "sparc_measure_fp32_peak")
 
 
@@ -59,6 +64,7 @@ def lib():
     L.sparc_step.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp]
     L.sparc_step_injected.argtypes = [vp, PP, PA, i32, i32, vp, vp]
     L.sparc_step_logged.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, i32, i32, vp]
+    L.sparc_step_sampled.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, i32, i32, vp, i32, vp]
     L.sparc_observe.argtypes = [vp, i32, i32, vp, vp]
     L.sparc_reduce_stats.argtypes = [vp, i32, i32, vp, vp]
     L.sparc_host_scratch_bytes.restype = sz

@@ -139,6 +139,42 @@ __global__ void observe_kernel(SparcStatePtrs S, int n_envs, int n_segments, flo
     }
 }
 
+// one warp per env: one row of the per-signal log (SimulationLogger signals, utils/logger.py:105-160,
+// base signal list of experiments/run_simulation.py:126-138) from the stored state, i.e. what
+// `getattr(state, name)` returns after the reference's step() of the same µs.  out: [SPARC_N_SIGNALS][n_envs]
+__global__ void sample_signals_kernel(SparcStatePtrs S, int n_envs, int n_segments, double *out)
+{
+    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
+    if (warp >= n_envs) return;
+    const float *row = S.T + (size_t)warp * S.n_pad;
+    float m = -3.0e38f;
+    for (int i = lane; i < n_segments; i += 32) m = fmaxf(m, row[i]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if (lane == 0) {
+        const int e = warp;
+        const size_t n = (size_t)n_envs;
+        const int fl = S.flags[e];
+        out[SPARC_SIG_TIME * n + e] = (double)S.time[e];
+        out[SPARC_SIG_VOLTAGE * n + e] = S.voltage[e];
+        out[SPARC_SIG_CURRENT * n + e] = S.current[e];
+        out[SPARC_SIG_WIRE_POSITION * n + e] = S.wire[e];
+        out[SPARC_SIG_WIRE_VELOCITY * n + e] = S.v[e];
+        out[SPARC_SIG_WORKPIECE_POSITION * n + e] = S.wp[e];
+        out[SPARC_SIG_TARGET_DELTA * n + e] = S.target_delta[e];
+        out[SPARC_SIG_DEBRIS_DENSITY * n + e] = S.debris_density[e];
+        out[SPARC_SIG_FLOW_RATE * n + e] = S.flow[e];
+        out[SPARC_SIG_IS_SHORT_CIRCUIT * n + e] = (fl & SPARC_F_SHORT) ? 1.0 : 0.0;
+        out[SPARC_SIG_SPARK_STATE * n + e] = (double)S.spark_state[e];
+        out[SPARC_SIG_MAX_TEMPERATURE * n + e] = (double)m;
+        out[SPARC_SIG_AVERAGE_TEMPERATURE * n + e] = S.wire_avg_T[e];
+        out[SPARC_SIG_DEBRIS_VOLUME * n + e] = S.debris_volume[e];
+        out[SPARC_SIG_TIME_IN_CRITICAL * n + e] = (double)S.crit_count[e];
+        out[SPARC_SIG_FLAGS * n + e] = (double)fl;
+    }
+}
+
 __global__ void reduce_stats_kernel(SparcStatePtrs S, int n_envs, double *out)
 {
     double acc[SPARC_N_STATS] = {0, 0, 0, 0, 0, 0, 0, 0};
@@ -221,7 +257,7 @@ int check_common(const void *state, const SparcParams *p, int n_envs)
 
 int launch_step(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
                 uint64_t seed, uint32_t env_id_base, const double *draws, void *stream, float *tlog = nullptr,
-                int log_every = 0, int n_log_envs = 0)
+                int log_every = 0, int n_log_envs = 0, double *signals = nullptr, int sample_every = 0)
 {
     int rc = check_common(state, p, n_envs);
     if (rc) return rc;
@@ -235,22 +271,35 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
     int blocks, threads;
     launch_geometry(v, n_envs, &blocks, &threads);
-    // one (mechanics pre-pass, fused step) pair per epoch of SPARC_MECH_EPOCH µs
-    for (int ep0 = 0; ep0 < n_us; ep0 += SPARC_MECH_EPOCH) {
+    // one (mechanics pre-pass, fused step) pair per chunk: at most SPARC_MECH_EPOCH µs, cut at every
+    // signal-sampling µs (the signal rows are read from the stored state between launches)
+    int t = 0;
+    while (t < n_us) {
+        int n = (n_us - t < SPARC_MECH_EPOCH) ? n_us - t : SPARC_MECH_EPOCH;
+        if (signals) {
+            const int to_sample = sample_every - t % sample_every;
+            if (n > to_sample) n = to_sample;
+        }
         sparc::StepArgs a;
         a.act = *actions;
         a.n_envs = n_envs;
-        a.n_us = (n_us - ep0 < SPARC_MECH_EPOCH) ? n_us - ep0 : SPARC_MECH_EPOCH;
+        a.n_us = n;
         a.seed = seed;
         a.env_id_base = env_id_base;
         a.draws = draws;
         a.tlog = tlog;
         a.log_every = log_every;
         a.n_log_envs = n_log_envs;
-        a.it_base = ep0;
+        a.it_base = t;
         a.total_us = n_us;
         sparc::mech_launch(*p, S, a, (cudaStream_t)stream);
         v->fn[tlog ? 1 : 0][draws ? 1 : 0]<<<blocks, threads, 0, (cudaStream_t)stream>>>(*p, S, a);
+        t += n;
+        if (signals && t % sample_every == 0) {
+            const int sthreads = 128, sblocks = (n_envs * 32 + sthreads - 1) / sthreads;
+            sample_signals_kernel<<<sblocks, sthreads, 0, (cudaStream_t)stream>>>(
+                S, n_envs, p->n_segments, signals + (size_t)(t / sample_every - 1) * SPARC_N_SIGNALS * n_envs);
+        }
     }
     CUDA_TRY(cudaGetLastError());
     return SPARC_OK;
@@ -328,6 +377,19 @@ int sparc_step_logged(void *state, const SparcParams *p, const SparcActions *act
     if (log_every <= 0 || n_log_envs < 0 || n_log_envs > n_envs) return fail(SPARC_E_INVALID, "bad log_every / n_log_envs");
     return launch_step(state, p, actions, n_envs, n_us, seed, env_id_base, draws_dev, stream, tlog_dev, log_every,
                        n_log_envs);
+}
+
+int sparc_step_sampled(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+                       uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *tlog_dev, int log_every,
+                       int n_log_envs, double *signals_dev, int sample_every, void *stream)
+{
+    if (!signals_dev || sample_every <= 0) return fail(SPARC_E_INVALID, "signal log needs a buffer and sample_every > 0");
+    if (tlog_dev) {
+        if (log_every <= 0) return fail(SPARC_E_INVALID, "temperature log needs log_every > 0");
+        if (n_log_envs < 0 || n_log_envs > n_envs) return fail(SPARC_E_INVALID, "n_log_envs out of range");
+    }
+    return launch_step(state, p, actions, n_envs, n_us, seed, env_id_base, draws_dev, stream, tlog_dev,
+                       tlog_dev ? log_every : 0, tlog_dev ? n_log_envs : 0, signals_dev, sample_every);
 }
 
 int sparc_observe(const void *state, int n_envs, int n_segments, float *obs_dev, void *stream)

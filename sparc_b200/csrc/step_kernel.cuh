@@ -159,7 +159,12 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     s.w_last_flow = S.w_last_flow[e];
     s.rand_short_rem = S.rand_short_rem[e]; s.deb_short_rem = S.deb_short_rem[e];
     s.current_mode = S.current_mode[e];
-    s.win_sparks = 0; s.win_short_us = 0;
+    // the per-call window (mean voltage, sparks, short µs of the last step call) carries over the
+    // launches of one call (it_base > 0: a later mechanics epoch / sampling chunk of the same call)
+    const bool cont = a.it_base > 0;
+    s.win_sparks = cont ? S.win_sparks[e] : 0;
+    const int win_short0 = cont ? S.win_short_us[e] : 0, win_steps0 = cont ? S.win_steps[e] : 0;
+    s.win_short_us = win_short0;
     s.dens_valid = true; s.pend_flush = false; s.fast_ok = false;
     s.tsi_prev = 0; s.plasma_idx = -1;
     s.heat_on = false; s.thermal = false; s.refresh = false; s.freeze = false; s.became_done = false;
@@ -169,7 +174,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
 
     double wp = S.wp[e], wire = S.wire[e], v = S.v[e], prev_accel = S.prev_accel[e];
     double target_delta = S.target_delta[e], voltage = S.voltage[e], debris_volume = S.debris_volume[e];
-    double win_vsum = 0.0, gap_prev = wp - wire;
+    double win_vsum = cont ? S.win_vsum[e] : 0.0, gap_prev = wp - wire;
     int time = S.time[e], spark_state = S.spark_state[e], spark_dur = S.spark_dur[e], flags = S.flags[e];
     int crit_count = S.crit_count[e];
     int w_zone_counter = S.w_zone_counter[e];
@@ -181,7 +186,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         s.plasma_idx = (P.segment_len != 0.0) ? P.zone_start + (int)py_floordiv(S.spark_y[e], P.segment_len) : P.zone_start;
 
     if (flags & SPARC_F_DONE) {                 // terminated envs are left untouched
-        if (s.writer) { S.win_vsum[e] = 0.0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0; }
+        if (s.writer && !cont) { S.win_vsum[e] = 0.0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0; }
         return;
     }
 
@@ -600,9 +605,9 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         S.crit_count[e] = crit_count;
         S.current_mode[e] = s.current_mode;
         S.w_zone_counter[e] = w_zone_counter; S.flags[e] = flags;
-        S.stat_short_us[e] += s.win_short_us;
+        S.stat_short_us[e] += s.win_short_us - win_short0;
         S.stat_steps[e] += win_steps;
-        S.win_sparks[e] = s.win_sparks; S.win_short_us[e] = s.win_short_us; S.win_steps[e] = win_steps;
+        S.win_sparks[e] = s.win_sparks; S.win_short_us[e] = s.win_short_us; S.win_steps[e] = win_steps0 + win_steps;
     }
 }
 

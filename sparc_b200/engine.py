@@ -150,6 +150,34 @@ class Engine:
                                                int(log_every), n_log, self._stream()))
         return out
 
+    def step_sampled(self, n_us: int, sample_every: int, draws: Optional[torch.Tensor] = None,
+                     log_every: int = 0, n_log_envs: Optional[int] = None):
+        """step() with the device-side signal logger: returns (signals, tlog) where signals is
+        [n_us // sample_every, N_SIGNALS, n_envs] float64 (rows of `_native.SIGNALS`, the state after
+        every `sample_every`-th µs, like SimulationLogger.collect after that step(), utils/logger.py:118-160)
+        and tlog the temperature log of step_logged (None unless log_every > 0)."""
+        every = int(sample_every)
+        assert every > 0
+        rows = int(n_us) // every
+        a = self._actions_struct(self._act_dev)
+        with torch.cuda.device(self.device):
+            sig = torch.zeros(rows, N.N_SIGNALS, self.n_envs, dtype=torch.float64, device=self.device)
+            tlog, n_log = None, 0
+            if log_every:
+                n_log = self.n_envs if n_log_envs is None else int(n_log_envs)
+                tlog = torch.zeros(n_log, int(n_us) // int(log_every), self.n_segments, dtype=torch.float32,
+                                   device=self.device)
+            dptr = None
+            if draws is not None:
+                assert draws.dtype == torch.float64 and draws.is_contiguous() and draws.device == self.blob.device
+                assert tuple(draws.shape) == (self.n_envs, int(n_us), N.N_DRAW_SLOTS)
+                dptr = draws.data_ptr()
+            N.check(self.lib.sparc_step_sampled(self.blob.data_ptr(), C.byref(self.params), C.byref(a), self.n_envs,
+                                                int(n_us), self.seed, self.env_id_base, dptr,
+                                                tlog.data_ptr() if tlog is not None else None, int(log_every), n_log,
+                                                sig.data_ptr(), every, self._stream()))
+        return sig, tlog
+
     def step_host(self, n_us: int) -> torch.Tensor:
         """Host-buffer path: pinned host actions -> device, n_us steps, observation -> pinned host.
 

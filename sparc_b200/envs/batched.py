@@ -89,14 +89,22 @@ class BatchedWireEDMEnv:
         return {k: o[i] for i, k in enumerate(OBS_KEYS)}
 
     def step(self, actions: Dict, n_us: Optional[int] = None, draws: Optional[torch.Tensor] = None,
-             log_temperature_every: Optional[int] = None, n_log_envs: Optional[int] = None):
+             log_temperature_every: Optional[int] = None, n_log_envs: Optional[int] = None,
+             log_signals_every: Optional[int] = None):
         """Advance every env by `n_us` µs (default: one control step).  Returns the Gymnasium
         5-tuple with batched tensors: obs dict of [n_envs] float32, reward [n_envs] (0.0 — the
-        reference's reward is a placeholder, wire_edm.py:185-187), terminated, truncated, info."""
+        reference's reward is a placeholder, wire_edm.py:185-187), terminated, truncated, info.
+
+        `log_signals_every=k` runs the device-side signal logger: `info["signal_log"]` maps each
+        name of `_native.SIGNALS` to a [n_us // k, n_envs] float64 tensor (k=1: the reference
+        logger's "every_step")."""
         n_us = self.servo_interval if n_us is None else int(n_us)
         self._stage(actions)
-        tlog = None
-        if log_temperature_every:
+        tlog, sig = None, None
+        if log_signals_every:
+            sig, tlog = self.engine.step_sampled(n_us, int(log_signals_every), draws,
+                                                 int(log_temperature_every or 0), n_log_envs)
+        elif log_temperature_every:
             tlog = self.engine.step_logged(n_us, int(log_temperature_every), n_log_envs, draws)
         else:
             self.engine.step(n_us, draws)
@@ -113,6 +121,8 @@ class BatchedWireEDMEnv:
         }
         if tlog is not None:
             info["wire_temperature_log"] = tlog     # [n_log_envs, n_us // every, n_segments]
+        if sig is not None:
+            info["signal_log"] = {name: sig[:, i] for i, name in enumerate(N.SIGNALS)}
         reward = torch.zeros(self.n_envs, dtype=torch.float32, device=self.device)
         truncated = torch.zeros(self.n_envs, dtype=torch.bool, device=self.device)
         if self.auto_reset:

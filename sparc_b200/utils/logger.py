@@ -7,7 +7,10 @@ every `BatchedWireEDMEnv.step()` (one control step), and each sample is a device
 batch: scalars -> [n_envs], `wire_temperature` -> [n_envs, n_segments].  Sub-control-step
 sampling of the temperature field comes from the kernel itself (`sparc_step_logged`): pass
 `log_temperature_every=k` to `BatchedWireEDMEnv.step` and the [n_envs, n_us/k, n_segments] block in
-`info["wire_temperature_log"]` is appended sample by sample.
+`info["wire_temperature_log"]` is appended sample by sample.  Sub-control-step sampling of the scalar
+signals ("every_step" / "interval" below one control step) comes from `sparc_step_sampled`: pass
+`log_signals_every=k` to `BatchedWireEDMEnv.step` (`step_kwargs()` gives both arguments for this
+logger's configuration) and the rows of `info["signal_log"]` are appended one per sampled µs.
 
 `.npz` layout: signal -> array [n_samples, n_envs(, n_segments)]; with one env the env axis is
 dropped, which is exactly the reference's `(n_timesteps, n_segments)` (animate_wire_heating.py:44-47).
@@ -83,15 +86,42 @@ class BatchedSimulationLogger:
             return eng["wire_avg_T"].clone()
         return None
 
+    # reference signal name -> row name of the device-side signal log (_native.SIGNALS)
+    _SIGLOG = {"time": "time", "voltage": "voltage", "current": "current", "wire_position": "wire_position",
+               "wire_velocity": "wire_velocity", "workpiece_position": "workpiece_position",
+               "target_delta": "target_delta", "debris_density": "debris_density",
+               "debris_concentration": "debris_density", "flow_rate": "flow_rate",
+               "dielectric_flow_rate": "flow_rate", "is_short_circuit": "is_short_circuit",
+               "spark_status": "spark_state", "wire_average_temperature": "wire_average_temperature",
+               "debris_volume": "debris_volume", "time_in_critical_temp": "time_in_critical_temp"}
+
+    def step_kwargs(self) -> Dict[str, int]:
+        """Keyword arguments for `BatchedWireEDMEnv.step` that make the kernel sample at this
+        logger's frequency: every µs for "every_step", every `value` µs for "interval" (when it
+        divides the control step), nothing for "control_step"."""
+        freq = self.config["log_frequency"]
+        k = 1 if freq["type"] == "every_step" else int(freq.get("value", 0)) if freq["type"] == "interval" else 0
+        if k <= 0 or (self.env is not None and self.env.servo_interval % k):
+            return {}
+        kw = {}
+        if any(n in self._SIGLOG for n in self.config["signals_to_log"]):
+            kw["log_signals_every"] = k
+        if "wire_temperature" in self.config["signals_to_log"]:
+            kw["log_temperature_every"] = k
+        return kw
+
     def collect(self, info: Optional[Dict[str, Any]] = None, n_us: Optional[int] = None):
         """Call after every `env.step()`.  `n_us` defaults to the env's control step."""
         if self.env is None:
             raise ValueError("BatchedSimulationLogger needs env_reference")
+        import torch
+
         n_us = int(self.env.servo_interval if n_us is None else n_us)
         before = self.step_counter
         self.step_counter += n_us
         freq = self.config["log_frequency"]
         tlog = (info or {}).get("wire_temperature_log")
+        slog = (info or {}).get("signal_log")
         if freq["type"] == "interval":
             k = int(freq["value"])
             should_log = self.step_counter // k > before // k
@@ -101,6 +131,15 @@ class BatchedSimulationLogger:
             if name == "wire_temperature" and tlog is not None:
                 for r in range(tlog.shape[1]):     # kernel-sampled rows, already at the requested interval
                     self.log_data[name].append(tlog[:, r])
+                continue
+            if slog is not None and name in self._SIGLOG:
+                rows = slog[self._SIGLOG[name]]    # kernel-sampled rows [n_samples, n_envs]
+                if name == "is_short_circuit":
+                    rows = rows != 0
+                elif name in ("time", "spark_status", "time_in_critical_temp"):
+                    rows = rows.to(dtype=torch.int32)
+                for r in range(rows.shape[0]):
+                    self.log_data[name].append(rows[r])
                 continue
             if not should_log:
                 continue

@@ -139,3 +139,40 @@ def test_batched_logger_npz_layout(tmp_path):
     np.testing.assert_array_equal(d["wire_position"][-1], venv.state_tensor("wire").cpu().numpy())
     with pytest.raises(ValueError):
         SimulationLogger({"signals_to_log": [], "log_frequency": {"type": "control_step"}, "backend": {"type": "memory"}})
+
+
+def test_logger_every_step_uses_the_device_signal_log(tmp_path):
+    """SimulationLogger "every_step": one sample per µs of scalars and of the temperature field,
+    produced inside the step call (reference: collect() after every step(), utils/logger.py:118-160)."""
+    import torch
+    from sparc_b200.utils import BatchedSimulationLogger
+
+    env = _env(3, seed=2)
+    env.reset()
+    path = str(tmp_path / "every_step.npz")
+    lg = BatchedSimulationLogger({"signals_to_log": ["time", "voltage", "wire_position", "is_short_circuit",
+                                                     "debris_concentration", "wire_temperature"],
+                                  "log_frequency": {"type": "every_step"},
+                                  "backend": {"type": "numpy", "filepath": path}}, env_reference=env)
+    kw = lg.step_kwargs()
+    assert kw == {"log_signals_every": 1, "log_temperature_every": 1}
+    act = env.constant_action(servo=0.1)
+    for _ in range(2):
+        _, _, _, _, info = env.step(act, **kw)
+        lg.collect(info)
+    lg.finalize()
+    d = np.load(path)
+    assert d["time"].shape == (2000, 3) and d["time"].dtype == np.int32
+    assert np.array_equal(d["time"][:, 0], np.arange(1, 2001))
+    assert d["wire_temperature"].shape == (2000, 3, env.n_segments)
+    assert d["is_short_circuit"].dtype == bool and d["voltage"].max() <= 80.0
+    # the last sample is the live state
+    assert np.array_equal(d["wire_position"][-1], env.state_tensor("wire").cpu().numpy())
+    assert np.array_equal(d["wire_temperature"][-1], env.wire_temperature.cpu().numpy())
+    # interval logging below one control step
+    lg2 = BatchedSimulationLogger({"signals_to_log": ["voltage"], "log_frequency": {"type": "interval", "value": 250},
+                                   "backend": {"type": "memory"}}, env_reference=env)
+    assert lg2.step_kwargs() == {"log_signals_every": 250}
+    _, _, _, _, info = env.step(act, **lg2.step_kwargs())
+    lg2.collect(info)
+    assert len(lg2.get_data()["voltage"]) == 4 and lg2.get_data()["voltage"][0].shape == (3,)

@@ -207,3 +207,54 @@ def test_long_launch_equals_split_launches():
             if name not in skip:
                 assert torch.equal(t, engs[1].fields[name]), name
         assert int(engs[0]["time"][0].item()) == 2500
+        assert int(engs[0]["win_steps"][0].item()) == 2500       # the window spans the epochs of one call
+        assert int(engs[1]["win_steps"][0].item()) == 500
+
+
+@pytest.mark.parametrize("name", ["cfg2_default", "debris_shorts"])
+def test_signal_log_matches_reference_golden(name):
+    """Device-side signal logger (sparc_step_sampled): every µs of the first 3000 µs in three
+    1000-µs calls, then every 50th µs, against the per-µs rows recorded from the unmodified
+    reference — what SimulationLogger("every_step" / "interval") would have stored."""
+    import torch
+    from sparc_b200 import _native as N
+
+    g = _golden(name)
+    case = CS.CASES[name]
+    tape = CS.case_tape(case)
+    actions = g["actions"]
+    rows = g["f64_rows"]
+    n_done = int(g["n_done"][0])
+    eng = PU.make_engine(case, n_envs=2)
+    draws = torch.from_numpy(np.stack([tape, tape])).to(eng.device)
+    S = {n: k for k, n in enumerate(N.SIGNALS)}
+    f_of = {"workpiece_position": 0, "wire_position": 1, "wire_velocity": 2, "voltage": 4, "current": 5,
+            "debris_volume": 6, "debris_density": 7, "flow_rate": 8}
+    i_of = {"time": 0, "spark_state": 4, "is_short_circuit": 6, "time_in_critical_temp": 10}
+    done, checked = 0, 0
+    # golden rows: every µs below 3000, then µs 3000, 3050, ...: a 1-µs call re-aligns the sampling phase
+    plan = [(1000, 1)] * 3 + [(1, 1)] + [(1000, 50)] * ((n_done - 3001) // 1000)
+    for n, every in plan:
+        PU.stage_action(eng, PU.action_for_window(actions, done, n))
+        sig, _ = eng.step_sampled(n, every, draws[:, done:done + n].contiguous())
+        sig = sig.cpu().numpy()
+        assert sig.shape == (n // every, N.N_SIGNALS, 2)
+        for r in range(sig.shape[0]):
+            us = done + (r + 1) * every - 1                 # last µs stepped before this sample
+            k = int(np.searchsorted(rows, us))
+            assert rows[k] == us
+            for env in range(2):
+                for nm, col in f_of.items():
+                    a, b = sig[r, S[nm], env], g["f64"][k, col]
+                    assert a == b or abs(a - b) <= PU.F64_RTOL * abs(b), (name, us, nm, a, b)
+                for nm, col in i_of.items():
+                    assert int(sig[r, S[nm], env]) == int(g["i32"][us, col]), (name, us, nm)
+                tm, tr = sig[r, S["max_wire_temperature"], env], g["f64"][k, 11]
+                assert abs(tm - tr) <= PU.T_ATOL + PU.T_RTOL * abs(tr), (name, us, tm, tr)
+            checked += 1
+        done += n
+        if int(eng["flags"][0].item()) & N.F_DONE:
+            break
+    assert checked >= 3000
+    # the per-call window spans the whole call even though it was cut into launches at the samples
+    assert int(eng["win_steps"][0].item()) == 1000 or int(eng["flags"][0].item()) & N.F_DONE
