@@ -16,7 +16,7 @@ __version__ = "0.1.0"
 
 def __getattr__(name):
     # envs/engine import torch; keep `import sparc_b200` light
-    if name in ("WireEDMEnv", "BatchedWireEDMEnv", "WireEDMVectorEnv"):
+    if name in ("WireEDMEnv", "BatchedWireEDMEnv", "GroupedWireEDMEnv", "WireEDMVectorEnv"):
         from . import envs
 
         return getattr(envs, name)
@@ -33,7 +33,7 @@ def __getattr__(name):
 
 __all__ = [
     "EDMState", "DeviceStateView", "crater_dtype", "EnvironmentConfig", "MaterialDatabase", "WireMaterial",
-    "get_material_db", "WireEDMEnv", "BatchedWireEDMEnv", "WireEDMVectorEnv", "GapController",
+    "get_material_db", "WireEDMEnv", "BatchedWireEDMEnv", "GroupedWireEDMEnv", "WireEDMVectorEnv", "GapController",
     "VoltageController", "Engine", "EDMModule",
     "IgnitionModule", "IgnitionModuleParameters", "WireModule", "WireModuleParameters",
     "MaterialRemovalModule", "MaterialModuleParameters", "DielectricModule", "DielectricModuleParameters",

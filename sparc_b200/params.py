@@ -109,6 +109,13 @@ class WireModuleParameters:
 @dataclass
 class MaterialModuleParameters:
     base_overcut: float = 0.12
+    # Extension (not in the reference dataclass): which crater record a current mode samples from.
+    #   "reference"    the record with the mode's own key; modes without one (even modes, I19) raise
+    #                  ValueError at their first spark (material.py:100-113) — the reference's behaviour;
+    #   "fill_missing" as above where a record exists, the documented current scaling elsewhere;
+    #   "documented"   every mode uses the scaling of docs/theory/material_theory.md:77-89:
+    #                  record = available[floor(r*(N-1))], r = (I_machine - I_min)/(I_max - I_min).
+    crater_mode_mapping: str = "reference"
 
 
 @dataclass
@@ -295,12 +302,22 @@ def derive_params(config: EnvironmentConfig, mechanics_control_mode: str = "posi
     # per-mode tables (ignition.py:98-113; material.py:100-123, 152-169)
     currents = load_currents()
     craters = load_craters()
+    mapping = getattr(mt, "crater_mode_mapping", "reference")
+    if mapping not in ("reference", "fill_missing", "documented"):
+        raise ValueError(f"crater_mode_mapping must be 'reference', 'fill_missing' or 'documented', got {mapping}")
+    avail = sorted(craters, key=lambda name: int(name[1:]))            # I1, I3, ..., I17
+    amps = [float(v["Current"]) for v in currents.values()]
+    i_min, i_max = min(amps), max(amps)
     for k in range(1, MAX_MODE + 1):
         key = f"I{k}"
         if key in currents:
             p.currents[k] = float(currents[key]["Current"])
-        if key in craters:
-            c = craters[key]
+        src = key if key in craters else None
+        if key in currents and (mapping == "documented" or (mapping == "fill_missing" and src is None)):
+            r = (float(currents[key]["Current"]) - i_min) / (i_max - i_min)
+            src = avail[min(int(math.floor(r * (len(avail) - 1))), len(avail) - 1)]
+        if src is not None:
+            c = craters[src]
             p.crater_mean[k] = float(c["ellipsoid_volume_half"])
             p.crater_std[k] = float(c["ellipsoid_volume_std"])
             kerf_width_mm = mt.base_overcut + config.wire_diameter + c["depth"] / 1000.0

@@ -103,3 +103,30 @@ def test_action_window_latch_timing():
     assert PU.action_for_window(acts, 2000, 1000) == "a1"
     assert PU.action_for_window(acts, 2999, 2) == "a2"
     assert PU.action_for_window(acts, 9000, 1000) == "a2"
+
+
+def test_crater_mode_mapping_extension():
+    """Opt-in crater record mapping: the default keeps the reference's table
+    (odd modes only, material.py:100-113); "documented" is docs/theory/material_theory.md:77-89."""
+    import math
+    import pytest
+    from sparc_b200 import params as P
+
+    cfg = P.EnvironmentConfig()
+    ref = P.derive_params(cfg, "position")
+    assert [k for k in range(20) if ref.crater_avail[k]] == [1, 3, 5, 7, 9, 11, 13, 15, 17]
+    fill = P.derive_params(cfg, "position", material=P.MaterialModuleParameters(crater_mode_mapping="fill_missing"))
+    doc = P.derive_params(cfg, "position", material=P.MaterialModuleParameters(crater_mode_mapping="documented"))
+    assert all(fill.crater_avail[k] and doc.crater_avail[k] for k in range(1, 20))
+    for k in (1, 3, 5, 17):                                   # existing records are kept by fill_missing
+        assert fill.crater_mean[k] == ref.crater_mean[k] and fill.kerf_times_height[k] == ref.kerf_times_height[k]
+    amps = [ref.currents[k] for k in range(1, 20)]
+    for k in range(1, 20):
+        r = (amps[k - 1] - 30.0) / (600.0 - 30.0)
+        src = 2 * min(int(math.floor(r * 8)), 8) + 1          # crater records I1, I3, ..., I17
+        assert doc.crater_mean[k] == ref.crater_mean[src] and doc.crater_std[k] == ref.crater_std[src]
+        if not ref.crater_avail[k]:
+            assert fill.crater_mean[k] == ref.crater_mean[src]
+    assert doc.crater_mean[13] == ref.crater_mean[5]          # "I13 = 215 A -> 5 A crater data" (run_simulation.py:44)
+    with pytest.raises(ValueError):
+        P.derive_params(cfg, "position", material=P.MaterialModuleParameters(crater_mode_mapping="nearest"))

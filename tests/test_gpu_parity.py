@@ -106,6 +106,32 @@ def test_even_mode_sets_error_flag():
     assert eng["time"].cpu().numpy().tolist() == [1500, 3000]
 
 
+def test_even_mode_with_crater_mapping_extension():
+    """crater_mode_mapping="fill_missing": an even mode sparks with the documented record instead of
+    freezing; the workpiece advance is that record's (material.py:152-174 arithmetic)."""
+    import torch
+    from sparc_b200 import _native as N
+
+    case = dict(config=CS.README_CFG, mode="position", material={"crater_mode_mapping": "fill_missing"})
+    eng = PU.make_engine(case, n_envs=2)
+    prm = PU.case_params(case)
+    tape = CS.never_ignite_tape(3000, ignite_at=(1500,))
+    tape[:, 4] = 0.25                                         # crater volume = mean + 0.25 std
+    draws = torch.from_numpy(np.stack([tape, tape])).to(eng.device)
+    eng.set_actions(0.0, 80.0, np.array([6, 5]), 3.0, 80.0)
+    for t0 in range(0, 3000, 1000):
+        eng.step(1000, draws[:, t0:t0 + 1000].contiguous())
+    flags = eng["flags"].cpu().numpy()
+    assert not (flags[0] & N.F_MODE_ERROR) and not (flags[1] & N.F_MODE_ERROR)
+    assert eng["time"].cpu().numpy().tolist() == [3000, 3000]
+    wp = eng["wp"].cpu().numpy()
+    for env, mode in ((0, 6), (1, 5)):
+        vol = prm.crater_mean[mode] + 0.25 * prm.crater_std[mode]
+        want = 50.0 + (vol / 1e9) / prm.kerf_times_height[mode] * 1000.0
+        assert abs(wp[env] - want) <= 1e-12 * want, (mode, wp[env], want)
+    assert prm.crater_mean[6] == prm.crater_mean[1]           # 68 A maps to the first record
+
+
 @pytest.mark.parametrize("cfg_name,n_us", [("cfg2_default", 30000), ("hot_break", 20000), ("debris_shorts", 12000)])
 def test_on_device_philox_matches_oracle_philox(cfg_name, n_us):
     """Production path (on-device Philox4x32-10 draws, quiet-µs fast path): the oracle implements

@@ -154,3 +154,51 @@ def test_vector_env_same_step_truncation_and_disabled():
     assert term.all() and np.all(info["time"] < 10000)                    # frozen once terminal, never reset
     with pytest.raises(ValueError):
         _short_episode_env(4, autoreset_mode="sometimes")
+
+
+def test_grouped_env_equals_separate_homogeneous_batches():
+    """Heterogeneous batch = groups of homogeneous ones on concurrent streams: every group evolves
+    exactly as a stand-alone BatchedWireEDMEnv with the same global env ids (different geometry,
+    segment count, control mode and kernel variant per group)."""
+    import torch
+    from sparc_b200 import (BatchedWireEDMEnv, EnvironmentConfig, GroupedWireEDMEnv, WireModuleParameters)
+
+    thick = dict(workpiece_height=50.0, wire_diameter=0.25, wire_material="brass", target_cutting_distance=800.0)
+    groups = [
+        dict(n_envs=96, config=EnvironmentConfig(**README), mechanics_control_mode="position"),
+        dict(n_envs=40, config=EnvironmentConfig(**thick), mechanics_control_mode="velocity"),
+        dict(n_envs=24, config=EnvironmentConfig(**thick), mechanics_control_mode="position",
+             wire_params=WireModuleParameters(segment_len=0.1)),
+    ]
+    genv = GroupedWireEDMEnv(groups, seed=21, env_id_base=1000)
+    assert genv.n_envs == 160 and [e.n_segments for e in genv.envs] == [375, 550, 1100]
+    assert genv.group_of(0) == 0 and genv.group_of(96) == 1 and genv.group_of(159) == 2
+    solo, base = [], 1000
+    for g in groups:
+        kw = dict(g)
+        n = kw.pop("n_envs")
+        solo.append(BatchedWireEDMEnv(n, seed=21, env_id_base=base, **kw))
+        base += n
+    obs, _ = genv.reset()                       # a reset starts a new episode (new Philox streams) ...
+    for env in solo:
+        env.reset()                             # ... so the stand-alone batches are reset once too
+    assert obs["gap"].shape == (160,)
+    servo = torch.linspace(-0.5, 0.5, 160, device=genv.device)
+    servo[96:136] *= 400.0                                              # velocity-mode group: µm/s
+    mode = torch.full((160,), 5, dtype=torch.int32, device=genv.device)
+    mode[::3] = 13
+    act = {"servo": servo, "generator_control": {"target_voltage": 80.0, "current_mode": mode, "ON_time": 3.0,
+                                                 "OFF_time": 40.0}}
+    for _ in range(5):
+        obs, rew, term, trunc, info = genv.step(act)
+        for sl, env in zip(genv.group_slices(), solo):
+            env.step({"servo": servo[sl], "generator_control": {"target_voltage": 80.0, "current_mode": mode[sl],
+                                                                 "ON_time": 3.0, "OFF_time": 40.0}})
+    assert obs["gap"].shape == (160,) and term.shape == (160,) and info["time"].shape == (160,)
+    for genv_e, env in zip(genv.envs, solo):
+        for name in ("wp", "wire", "v", "debris_volume", "time", "spark_state", "stat_sparks", "flags"):
+            assert torch.equal(genv_e.state_tensor(name), env.state_tensor(name)), name
+        assert torch.equal(genv_e.wire_temperature, env.wire_temperature)
+    assert torch.equal(genv.state_tensor("wp"), torch.cat([e.state_tensor("wp") for e in solo]))
+    st = genv.episode_stats()
+    assert st["env_us"] == 160 * 5000 and st["sparks"] > 0
