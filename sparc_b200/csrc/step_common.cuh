@@ -204,6 +204,94 @@ __device__ __forceinline__ void prepare_fast(EnvState &s, const SparcParams &P)
     s.fast_ok = ok;
 }
 
+// DielectricModule.update hysteresis (dielectric.py:118-137): recompute the flow condition only when
+// the gap or the debris density moved out of the band around the values of the last recomputation.
+__device__ __forceinline__ double flow_condition(const SparcParams &P, const double gap_um, const double density)
+{
+    double r = gap_um / P.reference_gap;
+    double gf = r * r * r;                                  // (gap/ref)**3
+    gf = (gf < 1.0) ? gf : 1.0;
+    double x = P.debris_obstruction_coeff * density;
+    double df;
+    if (x < 0.5) df = (1.0 - 0.5 * x) / (1.0 + 0.5 * x);                   // fast_exp Pade branch
+    else df = exp(-x);
+    return gf * df;
+}
+
+__device__ __forceinline__ bool dielectric_hysteresis(EnvState &s, const SparcParams &P, const double gap_um)
+{
+    if (fabs(gap_um - s.d_last_gap) > 0.01 || fabs(s.debris_density - s.d_last_density) > 0.001) {
+        s.flow = flow_condition(P, gap_um, s.debris_density);
+        s.d_last_gap = gap_um;
+        s.d_last_density = s.debris_density;
+        return true;
+    }
+    return false;
+}
+
+// WireModule.update convection refresh (wire.py:278-281, 349-374): new h_base / h_enh when the flow
+// condition moved by more than 0.01 since the last refresh; the caller rebuilds its coefficients.
+__device__ __forceinline__ void wire_convection_refresh(EnvState &s, const SparcParams &P, const SparcStatePtrs &S)
+{
+    if (fabs(s.flow - s.w_last_flow) > 0.01) {
+        double ve = P.convection_velocity_factor * S.unwind_v[s.e];
+        ve = (ve > -0.9) ? ve : -0.9;
+        double hb = P.base_convection_coefficient * (1.0 + ve);
+        double hfloor = 0.1 * P.base_convection_coefficient;
+        hb = (hb > hfloor) ? hb : hfloor;
+        double he = hb * (1.0 + P.convection_flow_enhancement * s.flow);
+        s.hb = (float)hb; s.he = (float)he; s.refresh = true;
+        if (s.writer) { S.h_base[s.e] = s.hb; S.h_enh[s.e] = s.he; }
+        s.w_last_flow = s.flow;
+    }
+}
+
+// Hysteresis refresh without the general µs.  The look-ahead stopped at a µs whose only failed
+// condition is a band (gap or debris density moved out of the fast-path band) while everything the
+// ignition module does on that µs is provably quiet: idle or rest state, no latch, no countdown, no
+// ignition, and — checked here against the density bound of the OLD band, which is what
+// _update_short_circuit_detection sees — no short circuit at gap g.  Then the reference's µs is a quiet
+// µs whose DielectricModule.update recomputes the flow: apply the pending flush of the previous µs,
+// evaluate the exact hysteresis condition, refresh, and re-centre the fast-path bands; the µs itself
+// then runs as the first µs of the next quiet run (its own flush is applied by that run, hence `no
+// pending flush` on return).  Returns false, with nothing modified, when the exact condition does not
+// ask for a refresh, when the new flow would also refresh the wire's convection coefficients, or when
+// the short-circuit side cannot be proven quiet: the caller takes the general µs.
+static __device__ __noinline__ bool light_refresh(EnvState &s, const SparcParams &P, const SparcStatePtrs &S, const double g,
+                                           double &debris_volume, const bool pending)
+{
+    const double M = 1e-9;
+    double need = (P.hard_short_gap > 0.001) ? P.hard_short_gap : 0.001;
+    if (P.random_short_max_probability > 0.0 && P.random_short_max_gap > need) need = P.random_short_max_gap;
+    if (!(g >= need + M) || !(P.sigmoid_steepness > 0.0)) return false;
+    double crit = P.base_critical_density + P.gap_coefficient * g;
+    crit = (P.max_critical_density < crit) ? P.max_critical_density : crit;
+    if (!(s.d_last_density + 0.001 < crit - SPARC_EXPO_SAFE / P.sigmoid_steepness - M)) return false;
+    double deb = debris_volume;
+    if (pending && s.flow > 0.001 && deb > 0.001) {         // flush of the previous µs (dielectric.py:139-144)
+        double nv = deb - P.debris_removal_per_us * s.flow;
+        deb = (nv > 0.0) ? nv : 0.0;
+    }
+    const double gap_um = (g > 0.001) ? g : 0.001;
+    const double cavity = P.cavity_volume_coeff * (gap_um * 0.001);
+    double dens = 0.0;
+    if (cavity > 0.0) { double d = deb / cavity; dens = (d < 1.0) ? d : 1.0; }
+    if (!(fabs(gap_um - s.d_last_gap) > 0.01 || fabs(dens - s.d_last_density) > 0.001)) return false;
+    const double flow = flow_condition(P, gap_um, dens);
+    // a flow change that also moves the wire's convection coefficients is left to the general µs
+    if (fabs(flow - s.w_last_flow) > 0.01) return false;
+    debris_volume = deb;
+    s.debris_volume = deb;
+    s.debris_density = dens;
+    s.dens_valid = true;
+    s.pend_flush = false;
+    s.flow = flow;
+    s.d_last_gap = gap_um;
+    s.d_last_density = dens;
+    prepare_fast(s, P);
+    return true;
+}
+
 // ----------------------------------------------------------------------------------------------
 // The general µs: everything before the thermal stencil, exactly in the reference's order
 // (wire_edm.py:117-127).  Rare (sparks, shorts, latches, hysteresis refreshes, first µs of a
@@ -370,32 +458,11 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
         s.debris_density = (d < 1.0) ? d : 1.0;
     } else s.debris_density = 0.0;
     s.dens_valid = true;
-    if (fabs(gap_um - s.d_last_gap) > 0.01 || fabs(s.debris_density - s.d_last_density) > 0.001) {
-        double r = gap_um / P.reference_gap;
-        double gf = r * r * r;                              // (gap/ref)**3
-        gf = (gf < 1.0) ? gf : 1.0;
-        double x = P.debris_obstruction_coeff * s.debris_density;
-        double df;
-        if (x < 0.5) df = (1.0 - 0.5 * x) / (1.0 + 0.5 * x);               // fast_exp Pade branch
-        else df = exp(-x);
-        s.flow = gf * df;
-        s.d_last_gap = gap_um;
-        s.d_last_density = s.debris_density;
-    }
+    dielectric_hysteresis(s, P, gap_um);
     s.pend_flush = true;                                    // flushing of this µs applied lazily
 
     // ---- WireModule.update, host part (wire.py:259-309, 349-374) -----------------------------
-    if (fabs(s.flow - s.w_last_flow) > 0.01) {
-        double ve = P.convection_velocity_factor * S.unwind_v[e];
-        ve = (ve > -0.9) ? ve : -0.9;
-        double hb = P.base_convection_coefficient * (1.0 + ve);
-        double hfloor = 0.1 * P.base_convection_coefficient;
-        hb = (hb > hfloor) ? hb : hfloor;
-        double he = hb * (1.0 + P.convection_flow_enhancement * s.flow);
-        s.hb = (float)hb; s.he = (float)he; s.refresh = true;
-        if (s.writer) { S.h_base[e] = s.hb; S.h_enh[e] = s.he; }
-        s.w_last_flow = s.flow;
-    }
+    wire_convection_refresh(s, P, S);
     if (current * current > 1e-6) {                         // wire.py:98-102
         const double f = P.temp_update_factor;
         double jf = f * (P.joule_geom_factor * (current * current) * P.rho_elec);

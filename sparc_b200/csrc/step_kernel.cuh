@@ -192,6 +192,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
 
     int next_latch = s.latch_time + P.servo_interval;
     bool fast_ok = false, ran_fast = false, zone_mean_written = false, done = false;
+    int skip_flush = 0;                         // 1: the next quiet run starts with no pending debris flush
     int tsi_break = -1;
 
     // upper bound of lambda(gap) = ln2/(a g^2 + b g + c) over all gaps (ignition.py:348-364): a
@@ -348,12 +349,16 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             const double g = wp - pre_l;
             if (!force_general && fast_ok && (spark_state == 0 || spark_state == -2)) {
                 const int off = lane - i;
-                bool ok = lane < nb && g >= s.gap_lo_f && g <= s.gap_hi_f;
-                // debris after at most off+1 deferred flushes (sequential rounding <= 32 ulp(1))
-                double deb_lo = debris_volume;
-                if (debris_volume > 0.001) deb_lo = debris_volume - (double)(off + 1) * s.flush_amt - 1e-14;
-                ok = ok && deb_lo >= s.lo_c * g && debris_volume <= s.hi_c * g;
-                ok = ok && !(post_l > wp + 100.0);              // collision µs (wire_edm.py:173-175)
+                // band conditions: the hysteresis bands of the last flow recomputation
+                auto in_band = [&]() {
+                    bool b = g >= s.gap_lo_f && g <= s.gap_hi_f;
+                    // debris after at most off+1 deferred flushes (sequential rounding <= 32 ulp(1))
+                    double deb_lo = debris_volume;
+                    if (debris_volume > 0.001) deb_lo = debris_volume - (double)(off + 1) * s.flush_amt - 1e-14;
+                    return b && deb_lo >= s.lo_c * g && debris_volume <= s.hi_c * g;
+                };
+                // everything else that makes a µs quiet
+                bool ok = lane < nb && !(post_l > wp + 100.0);  // collision µs (wire_edm.py:173-175)
                 if (spark_state == -2) {
                     off_tr = s.onoff_thr - spark_dur - 1;
                     if (off_tr < 0) off_tr = 0;
@@ -377,8 +382,21 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                     double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
                     ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
                 }
-                const unsigned stop = __ballot_sync(FULL, !ok) >> i;
+                unsigned stop = __ballot_sync(FULL, !(ok && in_band())) >> i;
                 n = stop ? __ffs(stop) - 1 : 32 - i;
+                if (n == 0 && ((__ballot_sync(FULL, ok) >> i) & 1u)) {
+                    // only a band failed on µs i: refresh the hysteresis state in place (light_refresh)
+                    const bool pending = ran_fast || s.pend_flush;
+                    if (light_refresh(s, P, S, __shfl_sync(FULL, g, i), debris_volume, pending)) {
+                        ran_fast = false;
+                        skip_flush = 1;         // the refreshed µs has no pending flush before it
+                        fast_ok = s.fast_ok;
+                        if (fast_ok) {
+                            stop = __ballot_sync(FULL, !(ok && in_band())) >> i;
+                            n = stop ? __ffs(stop) - 1 : 32 - i;
+                        }
+                    }
+                }
             }
             force_general = false;
 
@@ -415,8 +433,9 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 win_vsum += (double)n_idle * s.tv_eff;
                 if (debris_volume > 0.001 && s.flush_amt > 0.0) {
 #pragma unroll 1
-                    for (int k = 0; k < nx && debris_volume > 0.001; k++) debris_volume = debris_volume - s.flush_amt;
+                    for (int k = skip_flush; k < nx && debris_volume > 0.001; k++) debris_volume = debris_volume - s.flush_amt;
                 }
+                skip_flush = 0;
                 gap_prev = __shfl_sync(FULL, g, i + nx - 1);
                 ran_fast = true;
                 if (P.compute_zone_mean) w_zone_counter += nx;
@@ -440,6 +459,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             s.time = time; s.spark_state = spark_state; s.spark_dur = spark_dur; s.flags = flags;
             s.it = it + i;
             if (ran_fast) { s.dens_valid = false; s.pend_flush = true; ran_fast = false; }
+            skip_flush = 0;
             general_pre<INJECT>(s, P, S, a);
             wp = s.wp; target_delta = s.target_delta; voltage = s.voltage; debris_volume = s.debris_volume;
             win_vsum = s.win_vsum; gap_prev = s.gap_prev;
