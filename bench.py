@@ -12,6 +12,7 @@ re-executes itself under torch.distributed.run.  Rank 0 prints ONE JSON line.
 from __future__ import annotations
 
 import argparse
+import numpy as np
 import json
 import os
 import subprocess
@@ -281,22 +282,28 @@ def run_gpu_arm(args):
         stage = torch.empty(chunk, dtype=torch.float32, pin_memory=True)
         d2h_extra = flat.numel() * 4
 
+    servo_np = ha["servo"].numpy()                          # numpy view of the pinned action buffer
+
     def e2e_step(k, obs_prev):
         if controller is not None and obs_prev is not None:
-            torch.clamp(sign * 0.1 * (obs_prev[0] - 25.0), -1.0, 1.0, out=ha["servo"])
+            np.clip(sign * 0.1 * (obs_prev[0] - 25.0), -1.0, 1.0, out=servo_np)
         else:
-            ha["servo"].fill_(action[0] + 1e-4 * (k % 3))   # host-side action of this step
+            servo_np.fill(action[0] + 1e-4 * (k % 3))       # host-side action of this step
         if tlog is None:
-            return eng.step_host(si)                        # syncs; obs is pinned host memory
+            return eng.step_host(si).numpy()                # syncs; obs is pinned host memory (zero-copy view)
         eng.set_actions(ha["servo"], ha["target_voltage"], ha["current_mode"], ha["on_time"], ha["off_time"])
         eng.step_logged(si, log_every, out=tlog)
         for o in range(0, flat.numel(), chunk):
             n = min(chunk, flat.numel() - o)
             stage[:n].copy_(flat[o:o + n], non_blocking=True)
-        return eng.observe().cpu()                          # syncs
+        return eng.observe().cpu().numpy()                  # syncs
 
+    # same simulated window as the device arm: fresh episode, same number of warm-up control steps
+    # (the workload drifts as the gap closes, so the two arms must not run back to back on one state)
+    eng.reset()
+    eng.set_actions(*action)
     obs = None
-    for k in range(3):
+    for k in range(max(args.warmup, 3)):
         obs = e2e_step(k, obs)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

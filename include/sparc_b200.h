@@ -186,6 +186,12 @@ int sparc_step_sampled(void *state, const SparcParams *p, const SparcActions *ac
                        uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *tlog_dev, int log_every,
                        int n_log_envs, double *signals_dev, int sample_every, void *stream);
 
+/* sparc_step / sparc_step_injected (draws_dev NULL or not) with the observation summary below written
+ * by the step kernel's epilogue into obs_dev[SPARC_N_OBS][n_envs] — the same values sparc_observe
+ * would read back from the state, without the second launch. */
+int sparc_step_observe(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+                       uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *obs_dev, void *stream);
+
 /* Observation summary of the last step call, obs_dev[SPARC_N_OBS][n_envs] float32:
  * 0 gap [µm], 1 wire_velocity [µm/s], 2 mean voltage over the call [V], 3 sparks ignited in the
  * call, 4 short-circuit µs in the call, 5 max wire temperature [K], 6 debris_density, 7 flags. */

@@ -36,7 +36,7 @@ _lib = None
 # every symbol include/sparc_b200.h declares
 EXPORTS = ("sparc_abi_version", "sparc_last_error", "sparc_num_fields", "sparc_field_info",
            "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_step",
-           "sparc_step_injected", "sparc_step_logged", "sparc_step_sampled", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
+           "sparc_step_injected", "sparc_step_logged", "sparc_step_sampled", "sparc_step_observe", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
            "sparc_step_host", "sparc_host_action_pitch", "sparc_launch_info", "sparc_measure_fp32_peak")
 
 
@@ -65,6 +65,7 @@ def lib():
     L.sparc_step_injected.argtypes = [vp, PP, PA, i32, i32, vp, vp]
     L.sparc_step_logged.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, i32, i32, vp]
     L.sparc_step_sampled.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, i32, i32, vp, i32, vp]
+    L.sparc_step_observe.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, vp]
     L.sparc_observe.argtypes = [vp, i32, i32, vp, vp]
     L.sparc_reduce_stats.argtypes = [vp, i32, i32, vp, vp]
     L.sparc_host_scratch_bytes.restype = sz

@@ -7,7 +7,6 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
-#include <cstdlib>
 #include <cstring>
 
 #include "../../include/sparc_b200.h"
@@ -257,7 +256,8 @@ int check_common(const void *state, const SparcParams *p, int n_envs)
 
 int launch_step(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
                 uint64_t seed, uint32_t env_id_base, const double *draws, void *stream, float *tlog = nullptr,
-                int log_every = 0, int n_log_envs = 0, double *signals = nullptr, int sample_every = 0)
+                int log_every = 0, int n_log_envs = 0, double *signals = nullptr, int sample_every = 0,
+                float *obs = nullptr)
 {
     int rc = check_common(state, p, n_envs);
     if (rc) return rc;
@@ -292,6 +292,7 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
         a.n_log_envs = n_log_envs;
         a.it_base = t;
         a.total_us = n_us;
+        a.obs = (t + n >= n_us) ? obs : nullptr;    // the last launch of the call writes the observation
         sparc::mech_launch(*p, S, a, (cudaStream_t)stream);
         v->fn[tlog ? 1 : 0][draws ? 1 : 0]<<<blocks, threads, 0, (cudaStream_t)stream>>>(*p, S, a);
         t += n;
@@ -392,6 +393,16 @@ int sparc_step_sampled(void *state, const SparcParams *p, const SparcActions *ac
                        tlog_dev ? log_every : 0, tlog_dev ? n_log_envs : 0, signals_dev, sample_every);
 }
 
+int sparc_step_observe(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
+                       uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *obs_dev, void *stream)
+{
+    if (!obs_dev) return fail(SPARC_E_INVALID, "null observation buffer");
+    int rc = launch_step(state, p, actions, n_envs, n_us, seed, env_id_base, draws_dev, stream, nullptr, 0, 0, nullptr, 0,
+                         obs_dev);
+    if (rc || n_us > 0) return rc;
+    return sparc_observe(state, n_envs, p->n_segments, obs_dev, stream);
+}
+
 int sparc_observe(const void *state, int n_envs, int n_segments, float *obs_dev, void *stream)
 {
     if (!state || !obs_dev || n_envs <= 0 || n_segments <= 0) return fail(SPARC_E_INVALID, "bad observe arguments");
@@ -447,8 +458,9 @@ int sparc_step_host(void *state, const SparcParams *p, const SparcActions *ah, i
     float *obs_dev = (float *)(d + 5 * n);
     size_t bytes = (size_t)n_envs * 4;
     const char *h0 = (const char *)ah->servo;
-    if ((const char *)ah->target_voltage == h0 + n && (const char *)ah->current_mode == h0 + 2 * n &&
-        (const char *)ah->on_time == h0 + 3 * n && (const char *)ah->off_time == h0 + 4 * n) {
+    const bool packed = (const char *)ah->target_voltage == h0 + n && (const char *)ah->current_mode == h0 + 2 * n &&
+                        (const char *)ah->on_time == h0 + 3 * n && (const char *)ah->off_time == h0 + 4 * n;
+    if (packed) {
         // the five host arrays sit in one buffer with the scratch pitch (sparc_host_action_pitch): one copy
         CUDA_TRY(cudaMemcpyAsync(d, h0, 4 * n + bytes, cudaMemcpyHostToDevice, st));
     } else {
@@ -458,10 +470,13 @@ int sparc_step_host(void *state, const SparcParams *p, const SparcActions *ah, i
         CUDA_TRY(cudaMemcpyAsync((void *)ad.on_time, ah->on_time, bytes, cudaMemcpyHostToDevice, st));
         CUDA_TRY(cudaMemcpyAsync((void *)ad.off_time, ah->off_time, bytes, cudaMemcpyHostToDevice, st));
     }
-    rc = launch_step(state, p, &ad, n_envs, n_us, seed, env_id_base, nullptr, stream);
+    // the observation is written by the step kernel's epilogue (same values as sparc_observe)
+    rc = launch_step(state, p, &ad, n_envs, n_us, seed, env_id_base, nullptr, stream, nullptr, 0, 0, nullptr, 0, obs_dev);
     if (rc) return rc;
-    rc = sparc_observe(state, n_envs, p->n_segments, obs_dev, stream);
-    if (rc) return rc;
+    if (n_us == 0) {
+        rc = sparc_observe(state, n_envs, p->n_segments, obs_dev, stream);
+        if (rc) return rc;
+    }
     CUDA_TRY(cudaMemcpyAsync(obs_host, obs_dev, bytes * SPARC_N_OBS, cudaMemcpyDeviceToHost, st));
     CUDA_TRY(cudaStreamSynchronize(st));
     return SPARC_OK;

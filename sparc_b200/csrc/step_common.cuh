@@ -90,6 +90,7 @@ struct StepArgs {
     float *tlog;             // temperature-field log [n_log_envs][total_us / log_every][n_segments] or NULL
     int log_every, n_log_envs;
     int it_base, total_us;   // this launch covers µs [it_base, it_base + n_us) of a call of total_us µs
+    float *obs;              // observation summary [SPARC_N_OBS][n_envs] written by the kernel epilogue, or NULL
 };
 
 #ifndef SPARC_BLOCK_THREADS

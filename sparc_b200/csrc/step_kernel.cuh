@@ -206,6 +206,30 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
 
     if (flags & SPARC_F_DONE) {                 // terminated envs are left untouched
         if (s.writer && !cont) { S.win_vsum[e] = 0.0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0; }
+        if (a.obs) {                            // observation of a frozen env, from the stored state
+            float m = -3.0e38f;
+            const float *row = S.T + (size_t)e * S.n_pad;
+            for (int c = gl; c < P.n_segments; c += 32 * W) m = fmaxf(m, row[c]);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
+            if constexpr (W > 1) {
+                if (lane == 0) sm_red[ctx.wid] = (double)m;
+                __syncthreads();
+                for (int w = 0; w < W; w++) m = fmaxf(m, (float)sm_red[w]);
+            }
+            if (s.writer) {
+                const size_t ne = (size_t)a.n_envs;
+                const int steps = cont ? win_steps0 : 0;
+                a.obs[0 * ne + e] = (float)(wp - wire);
+                a.obs[1 * ne + e] = (float)v;
+                a.obs[2 * ne + e] = steps > 0 ? (float)(win_vsum / (double)steps) : 0.0f;
+                a.obs[3 * ne + e] = (float)s.win_sparks;
+                a.obs[4 * ne + e] = (float)s.win_short_us;
+                a.obs[5 * ne + e] = m;
+                a.obs[6 * ne + e] = (float)s.debris_density;
+                a.obs[7 * ne + e] = (float)flags;
+            }
+        }
         return;
     }
 
@@ -649,6 +673,32 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         S.stat_short_us[e] += s.win_short_us - win_short0;
         S.stat_steps[e] += win_steps;
         S.win_sparks[e] = s.win_sparks; S.win_short_us[e] = s.win_short_us; S.win_steps[e] = win_steps0 + win_steps;
+    }
+    // ---------------- observation summary (what sparc_observe computes from the stored state) ----
+    if (a.obs) {
+        float m = spoolf;                       // cell 0; pad slots never exceed the real maximum
+#pragma unroll
+        for (int j = 0; j < H; j++) m = fmaxf(m, fmaxf(T[j].x, T[j].y));
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
+        if constexpr (W > 1) {
+            __syncthreads();
+            if (lane == 0) sm_red[ctx.wid] = (double)m;
+            __syncthreads();
+            for (int w = 0; w < W; w++) m = fmaxf(m, (float)sm_red[w]);
+        }
+        if (gl == 0) {
+            const size_t ne = (size_t)a.n_envs;
+            const int steps = S.win_steps[e];
+            a.obs[0 * ne + e] = (float)(wp - wire);
+            a.obs[1 * ne + e] = (float)v;
+            a.obs[2 * ne + e] = steps > 0 ? (float)(win_vsum / (double)steps) : 0.0f;
+            a.obs[3 * ne + e] = (float)s.win_sparks;
+            a.obs[4 * ne + e] = (float)s.win_short_us;
+            a.obs[5 * ne + e] = m;
+            a.obs[6 * ne + e] = (float)s.debris_density;
+            a.obs[7 * ne + e] = (float)flags;
+        }
     }
 }
 

@@ -113,20 +113,31 @@ class Engine:
                               bufs["current_mode"].data_ptr(), bufs["on_time"].data_ptr(),
                               bufs["off_time"].data_ptr())
 
-    def step(self, n_us: int, draws: Optional[torch.Tensor] = None) -> None:
+    def step(self, n_us: int, draws: Optional[torch.Tensor] = None, observe: bool = False):
         """Advance every env by n_us reference step() calls with the staged device actions.
 
-        draws: optional [n_envs, n_us, 5] float64 device tensor of injected random draws."""
+        draws: optional [n_envs, n_us, 5] float64 device tensor of injected random draws.
+        observe=True also returns the [8, n_envs] observation tensor of `observe()`, written by the
+        step kernel itself (no second launch)."""
         a = self._actions_struct(self._act_dev)
+        dptr = None
+        if draws is not None:
+            assert draws.dtype == torch.float64 and draws.is_contiguous() and draws.device == self.blob.device
+            assert tuple(draws.shape) == (self.n_envs, int(n_us), N.N_DRAW_SLOTS)
+            dptr = draws.data_ptr()
         with torch.cuda.device(self.device):
+            if observe:
+                N.check(self.lib.sparc_step_observe(self.blob.data_ptr(), C.byref(self.params), C.byref(a), self.n_envs,
+                                                    int(n_us), self.seed, self.env_id_base, dptr,
+                                                    self.obs_dev.data_ptr(), self._stream()))
+                return self.obs_dev
             if draws is None:
                 N.check(self.lib.sparc_step(self.blob.data_ptr(), C.byref(self.params), C.byref(a), self.n_envs,
                                             int(n_us), self.seed, self.env_id_base, self._stream()))
             else:
-                assert draws.dtype == torch.float64 and draws.is_contiguous() and draws.device == self.blob.device
-                assert tuple(draws.shape) == (self.n_envs, int(n_us), N.N_DRAW_SLOTS)
                 N.check(self.lib.sparc_step_injected(self.blob.data_ptr(), C.byref(self.params), C.byref(a),
-                                                     self.n_envs, int(n_us), draws.data_ptr(), self._stream()))
+                                                     self.n_envs, int(n_us), dptr, self._stream()))
+        return None
 
     def step_logged(self, n_us: int, log_every: int, n_log_envs: Optional[int] = None,
                     draws: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:

@@ -100,15 +100,15 @@ class BatchedWireEDMEnv:
         logger's "every_step")."""
         n_us = self.servo_interval if n_us is None else int(n_us)
         self._stage(actions)
-        tlog, sig = None, None
+        tlog, sig, fused = None, None, None
         if log_signals_every:
             sig, tlog = self.engine.step_sampled(n_us, int(log_signals_every), draws,
                                                  int(log_temperature_every or 0), n_log_envs)
         elif log_temperature_every:
             tlog = self.engine.step_logged(n_us, int(log_temperature_every), n_log_envs, draws)
         else:
-            self.engine.step(n_us, draws)
-        obs = self._obs()
+            fused = self.engine.step(n_us, draws, observe=True)     # observation from the kernel epilogue
+        obs = self._obs() if fused is None else {k: fused[i] for i, k in enumerate(OBS_KEYS)}
         flags = self.engine["flags"]
         terminated = (flags & N.F_DONE) != 0
         info = {

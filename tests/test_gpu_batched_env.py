@@ -176,3 +176,33 @@ def test_logger_every_step_uses_the_device_signal_log(tmp_path):
     _, _, _, _, info = env.step(act, **lg2.step_kwargs())
     lg2.collect(info)
     assert len(lg2.get_data()["voltage"]) == 4 and lg2.get_data()["voltage"][0].shape == (3,)
+
+
+@pytest.mark.parametrize("seg_len", [0.2, 0.05])
+def test_fused_observation_equals_observe_kernel(seg_len):
+    """The observation written by the step kernel's epilogue (sparc_step_observe, sparc_step_host) is
+    bit-identical to sparc_observe on the stored state: one warp per env (N=375) and several warps
+    per env (N=2200), running and terminated envs, and the host-buffer path."""
+    import torch
+    from sparc_b200 import BatchedWireEDMEnv, EnvironmentConfig, WireModuleParameters
+
+    cfg = dict(README, target_cutting_distance=50.002) if seg_len == 0.2 else \
+        dict(workpiece_height=50.0, wire_diameter=0.25, wire_material="brass", target_cutting_distance=50.0005)
+    env = BatchedWireEDMEnv(96, config=EnvironmentConfig(**cfg), seed=4,
+                            wire_params=WireModuleParameters(segment_len=seg_len))
+    env.reset()
+    act = env.constant_action(servo=0.3, current_mode=13, OFF_time=30.0)
+    saw_done = False
+    for k in range(6):
+        obs, _, term, _, _ = env.step(act)
+        fused = torch.stack([obs[key] for key in obs]).clone()
+        ref = env.engine.observe()[:7].clone()
+        assert torch.equal(fused, ref), k
+        saw_done = saw_done or bool(term.any())
+    assert saw_done and not bool(term.all())
+    # host-buffer path: observation from the epilogue, copied to pinned host memory
+    ha = env.engine.host_actions
+    ha["servo"].fill_(0.3); ha["target_voltage"].fill_(80.0); ha["current_mode"].fill_(13)
+    ha["on_time"].fill_(3.0); ha["off_time"].fill_(30.0)
+    oh = env.step_host().clone()
+    assert torch.equal(oh, env.engine.observe().cpu())
