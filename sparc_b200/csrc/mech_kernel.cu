@@ -48,9 +48,13 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
                                                    const __grid_constant__ SparcStatePtrs S,
                                                    const __grid_constant__ StepArgs a)
 {
+    // Let the step kernel start NOW (programmatic dependent launch): it is launched once every block
+    // of this grid has executed this instruction (or exited), i.e. once all producers are resident,
+    // and then follows this kernel block by block through mech_prog — it never waits for the grid.
+    asm volatile("griddepcontrol.launch_dependents;");
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= a.n_envs) return;
-    if (S.flags[e] & SPARC_F_DONE) return;
+    if (S.flags[e] & SPARC_F_DONE) return;      // the step kernel does not read the scratch of a frozen env
     double wire = S.wire[e], v = S.v[e], pa = S.prev_accel[e];
     const double d_old = S.target_delta[e];
     const double d_new = (double)a.act.servo[e];
@@ -59,11 +63,12 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
     if (first_latch < 0) first_latch = 0;
     double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
     double *ck = S.mech_ckpt + (size_t)e * SPARC_MECH_NCKPT * 2;
+    uint32_t *prog = (uint32_t *)S.mech_prog + e;
+    ck[0] = v;                                  // checkpoint c = state before µs c*SPARC_MECH_CKPT
+    ck[1] = pa;
 #pragma unroll 1
     for (int it0 = 0; it0 < a.n_us; it0 += SPARC_MECH_CKPT) {
         const int nb = (a.n_us - it0 < SPARC_MECH_CKPT) ? a.n_us - it0 : SPARC_MECH_CKPT;
-        ck[2 * (it0 / SPARC_MECH_CKPT)] = v;
-        ck[2 * (it0 / SPARC_MECH_CKPT) + 1] = pa;
         const double w0 = wire, v0 = v, p0 = pa;
         const bool ok = (P.control_mode == 0)
                             ? mech_block_fast<0>(P, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj)
@@ -76,9 +81,16 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
                 traj[it0 + k] = wire;
             }
         }
+        const int b = it0 / SPARC_MECH_CKPT + 1;        // blocks finished
+        ck[2 * b] = v;                                  // also what a rewind to the block boundary reads
+        ck[2 * b + 1] = pa;
+        if (it0 + nb >= a.n_us) {                       // end-of-launch pair
+            ck[2 * (SPARC_MECH_NCKPT - 1)] = v;
+            ck[2 * (SPARC_MECH_NCKPT - 1) + 1] = pa;
+        }
+        // publish: positions of µs < it0 + nb and checkpoints <= b are final (release at GPU scope)
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(prog), "r"(a.mech_seq + (uint32_t)b) : "memory");
     }
-    ck[2 * (SPARC_MECH_NCKPT - 1)] = v;                 // end-of-launch pair
-    ck[2 * (SPARC_MECH_NCKPT - 1) + 1] = pa;
 }
 
 void mech_launch(const SparcParams &P, const SparcStatePtrs &S, const StepArgs &a, cudaStream_t stream)

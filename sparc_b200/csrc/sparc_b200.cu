@@ -7,12 +7,14 @@
 #include <cuda_runtime.h>
 
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "../../include/sparc_b200.h"
 #include "state_layout.h"
 #include "step_common.cuh"
 #include "step_variants.h"
+#include <atomic>
 
 namespace {
 
@@ -50,9 +52,10 @@ const FieldDesc kFields[] = {
     {"T", 'f', sizeof(float)},
     {"mech_traj", 'd', sizeof(double)},
     {"mech_ckpt", 'd', sizeof(double)},
+    {"mech_prog", 'i', sizeof(int32_t)},
 };
 constexpr int kNumFields = (int)(sizeof(kFields) / sizeof(kFields[0]));
-constexpr int kFieldT = kNumFields - 3, kFieldTraj = kNumFields - 2, kFieldCkpt = kNumFields - 1;
+constexpr int kFieldT = kNumFields - 4, kFieldTraj = kNumFields - 3, kFieldCkpt = kNumFields - 2;
 
 constexpr size_t kAlign = 256;
 
@@ -86,6 +89,7 @@ SparcStatePtrs make_ptrs(void *state, int n_envs, int n_segments)
     S.T = (float *)(base + field_offset(idx++, n_envs, n_segments));
     S.mech_traj = (double *)(base + field_offset(idx++, n_envs, n_segments));
     S.mech_ckpt = (double *)(base + field_offset(idx++, n_envs, n_segments));
+    S.mech_prog = (int32_t *)(base + field_offset(idx++, n_envs, n_segments));
     S.n_pad = padded_segments(n_segments);
     return S;
 }
@@ -101,6 +105,7 @@ __global__ void reset_kernel(const __grid_constant__ SparcParams P, SparcStatePt
     SPARC_STATE_FIELDS(X)
 #undef X
     S.episode[e] = first_time ? 0 : S.episode[e] + 1;
+    S.mech_prog[e] = 0;
 }
 
 __global__ void reset_T_kernel(SparcStatePtrs S, int n_envs, float spool, const uint8_t *mask)
@@ -254,6 +259,16 @@ int check_common(const void *state, const SparcParams *p, int n_envs)
     return SPARC_OK;
 }
 
+// Tag of one (pre-pass, step) launch pair: progress values are tag + blocks published, so a value
+// left behind by an earlier launch can never be mistaken for progress of this one.
+uint32_t next_mech_seq()
+{
+    static std::atomic<uint32_t> counter{0};
+    uint32_t s;
+    do { s = (counter.fetch_add(1) + 1) & 0x3ffffffu; } while (s == 0);
+    return s << 6;
+}
+
 int launch_step(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
                 uint64_t seed, uint32_t env_id_base, const double *draws, void *stream, float *tlog = nullptr,
                 int log_every = 0, int n_log_envs = 0, double *signals = nullptr, int sample_every = 0,
@@ -293,8 +308,28 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
         a.it_base = t;
         a.total_us = n_us;
         a.obs = (t + n >= n_us) ? obs : nullptr;    // the last launch of the call writes the observation
+        // The pre-pass and the step kernel OVERLAP: mech_kernel triggers programmatic launch completion
+        // in its first instruction, so the step kernel (launched with programmatic stream
+        // serialization) starts as soon as every pre-pass block is resident, and consumes the
+        // trajectory block by block behind per-env progress tags (mech_prog) instead of waiting
+        // for the pre-pass grid to drain.
+        a.mech_seq = next_mech_seq();
         sparc::mech_launch(*p, S, a, (cudaStream_t)stream);
-        v->fn[tlog ? 1 : 0][draws ? 1 : 0]<<<blocks, threads, 0, (cudaStream_t)stream>>>(*p, S, a);
+        {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3((unsigned)blocks);
+            cfg.blockDim = dim3((unsigned)threads);
+            cfg.dynamicSmemBytes = 0;
+            cfg.stream = (cudaStream_t)stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr[0].val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = attr;
+            // SPARC_NO_PDL=1 (diagnostics): plain stream order, the step kernel starts after the pre-pass
+            static const bool no_pdl = getenv("SPARC_NO_PDL") != nullptr;
+            cfg.numAttrs = no_pdl ? 0 : 1;
+            CUDA_TRY(cudaLaunchKernelEx(&cfg, v->fn[tlog ? 1 : 0][draws ? 1 : 0], *p, S, a));
+        }
         t += n;
         if (signals && t % sample_every == 0) {
             const int sthreads = 128, sblocks = (n_envs * 32 + sthreads - 1) / sthreads;

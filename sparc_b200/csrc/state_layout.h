@@ -70,8 +70,8 @@
     X(win_short_us, int32_t, 'i', 0)                                                              \
     X(win_steps, int32_t, 'i', 0)
 
-// Mechanics look-ahead scratch (written by mech_kernel, read by the step kernel in the same call;
-// carries nothing between calls): wire position after each µs of a launch epoch, and
+// Mechanics look-ahead scratch (written by mech_kernel, read by the step kernel WHILE the pre-pass is
+// still running — the two kernels overlap, see mech_kernel.cu; carries nothing between calls): wire position after each µs of a launch epoch, and
 // (velocity, prev_accel) checkpoints every SPARC_MECH_CKPT µs plus the end-of-epoch pair.
 #define SPARC_MECH_EPOCH 1024
 #define SPARC_MECH_CKPT 32
@@ -86,6 +86,7 @@ struct SparcStatePtrs {
     float *T;       // [n_envs][n_pad]
     double *mech_traj;   // [n_envs][SPARC_MECH_EPOCH]
     double *mech_ckpt;   // [n_envs][SPARC_MECH_NCKPT][2]
+    int32_t *mech_prog;  // [n_envs] launch tag + number of SPARC_MECH_CKPT-µs blocks the pre-pass has published
     int32_t n_pad;
 };
 

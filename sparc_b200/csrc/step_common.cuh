@@ -91,6 +91,7 @@ struct StepArgs {
     int log_every, n_log_envs;
     int it_base, total_us;   // this launch covers µs [it_base, it_base + n_us) of a call of total_us µs
     float *obs;              // observation summary [SPARC_N_OBS][n_envs] written by the kernel epilogue, or NULL
+    uint32_t mech_seq;       // tag of this launch pair in SparcStatePtrs::mech_prog (multiple of 64)
 };
 
 #ifndef SPARC_BLOCK_THREADS

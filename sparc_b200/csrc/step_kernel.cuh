@@ -147,6 +147,22 @@ constexpr int min_blocks_for(int K)
 
 #define SPARC_LN2_UP 0.6931471805599460    /* ln2*(1+2^-50): u3 < fl(ln2/den) implies u3*den <= this */
 
+// Wait until the mechanics pre-pass of THIS launch (tag `seq`) has published at least `need` blocks of
+// the env whose progress word is *pp; returns the number published.  Out of line: it runs a handful
+// of times per launch and must not cost the step kernel registers.
+static __device__ __noinline__ uint32_t mech_wait(const uint32_t *pp, const uint32_t seq, const uint32_t need)
+{
+    unsigned spins = 0;
+    for (;;) {
+        uint32_t pv;
+        asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(pv) : "l"(pp) : "memory");
+        const uint32_t d = pv - seq;
+        if (d < 64u && d >= need) return d;
+        __nanosleep(100);
+        if (++spins > (1u << 23)) __trap();     // ~1 s: the producer is gone — fail loudly, never hang
+    }
+}
+
 template <int K, bool INJECT, int W, bool LOG>
 __global__ void __launch_bounds__(W == 1 ? SPARC_BLOCK_THREADS : 32 * W, W == 1 ? min_blocks_for(K) : 1)
 step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
@@ -342,8 +358,19 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         }
     };
 
-    // mechanics pre-pass results of this launch (mech_kernel)
+    // mechanics pre-pass results of this launch (mech_kernel).  The pre-pass is STILL RUNNING while this
+    // kernel executes (programmatic dependent launch, sparc_b200.cu): positions and checkpoints are
+    // read only after the producer thread of this env has published them through mech_prog
+    // (st.release / ld.acquire at GPU scope), and with ld.global.cg — an L1 line fetched before the
+    // producer finished it would be stale.  The producer is ~8x faster than this consumer, so after the
+    // first blocks one poll covers many blocks (mech_ready caches the last value seen; the poll
+    // itself is out of line, mech_wait).
     const double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
+    uint32_t mech_ready = 0;                    // pre-pass blocks known to be published
+    auto need_mech = [&](int upto_us) {         // positions of launch-µs < upto_us and checkpoints up to there
+        const uint32_t need = (uint32_t)((upto_us + SPARC_MECH_CKPT - 1) / SPARC_MECH_CKPT);
+        if (need > mech_ready) mech_ready = mech_wait((const uint32_t *)S.mech_prog + e, a.mech_seq, need);
+    };
     const double wire0 = wire, delta_old0 = target_delta, delta_new0 = (double)a.act.servo[e];
     const int first_latch_it = (next_latch - time > 0) ? next_latch - time : 0;
 
@@ -360,11 +387,10 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         }
         if (nb > to_latch) nb = to_latch;       // a block never straddles a latch
         // wire positions of this block from the mechanics pre-pass: lane l holds µs it + l
-        const double post_l = traj[it + ((lane < nb) ? lane : nb - 1)];  // wire after µs `lane`
-        // the next block's positions: start the L2/DRAM fetch now (no register held across the block)
-        if (it + nb + lane < a.n_us) asm volatile("prefetch.global.L1 [%0];" ::"l"(traj + it + nb + lane));
+        need_mech(it + nb);
+        const double post_l = __ldcg(traj + it + ((lane < nb) ? lane : nb - 1));  // wire after µs `lane`
         double pre_l = __shfl_up_sync(FULL, post_l, 1);                  // wire before µs `lane`
-        if (lane == 0) pre_l = (it == 0) ? wire0 : traj[it - 1];
+        if (lane == 0) pre_l = (it == 0) ? wire0 : __ldcg(traj + it - 1);
         // ignition roll of µs `lane` (slot 2): word (time+lane)&3 of Philox block (time+lane)>>2
         uint32_t w_l = 0;
         if (!INJECT) {
@@ -379,8 +405,8 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             const int target = it + steps;
             const int c = target / SPARC_MECH_CKPT;
             const double *ck = S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + c) * 2;
-            wire = (c == 0) ? wire0 : traj[c * SPARC_MECH_CKPT - 1];
-            v = ck[0]; prev_accel = ck[1];
+            wire = (c == 0) ? wire0 : __ldcg(traj + c * SPARC_MECH_CKPT - 1);
+            v = __ldcg(ck); prev_accel = __ldcg(ck + 1);
 #pragma unroll 1
             for (int k = c * SPARC_MECH_CKPT; k < target; k++)
                 mech_step(P, wire, v, prev_accel, (k >= first_latch_it) ? delta_new0 : delta_old0);
@@ -611,9 +637,10 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         it += nb;
     }
     if (!done) {                                // end-of-launch mechanics state from the pre-pass
-        wire = traj[a.n_us - 1];
-        v = S.mech_ckpt[((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2];
-        prev_accel = S.mech_ckpt[((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2 + 1];
+        need_mech(a.n_us);
+        wire = __ldcg(traj + a.n_us - 1);
+        v = __ldcg(S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2);
+        prev_accel = __ldcg(S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2 + 1);
     }
     if (LOG && logging && done) {               // rows sampled at or after termination: the frozen field
         for (int r = log_row; r < log_rows; r++) write_log_row(r);

@@ -222,7 +222,8 @@ class Engine:
 
     def bytes_per_control_step(self) -> int:
         """Algorithmic HBM bytes one step call moves: the whole state read once and written once."""
-        scratch = sum(int(self.fields[k].numel()) * 8 for k in ("mech_traj", "mech_ckpt") if k in self.fields)
+        scratch = sum(int(self.fields[k].numel()) * self.fields[k].element_size()
+                      for k in ("mech_traj", "mech_ckpt", "mech_prog") if k in self.fields)
         return 2 * (int(self.blob.numel()) - scratch)
 
 

@@ -44,8 +44,10 @@ def test_params_struct_size_matches_c(native):
     assert dt == "f" and cnt == 1000 * native.lib().sparc_padded_segments(375)
     # mechanics pre-pass scratch: wire trajectory of one 1024-µs epoch + (v, prev_accel) checkpoints
     assert by_name["mech_traj"][3] == 1000 * 1024 and by_name["mech_ckpt"][3] == 1000 * 33 * 2
+    # per-env progress tags of the overlapped pre-pass (int32)
+    assert by_name["mech_prog"][1] == "i" and by_name["mech_prog"][3] == 1000
     name, dt, off, cnt = tab[-1]
-    assert native.lib().sparc_state_bytes(1000, 375) >= off + cnt * 8
+    assert native.lib().sparc_state_bytes(1000, 375) >= off + cnt * {"d": 8, "f": 4, "i": 4}[dt]
     assert C.sizeof(SparcParams) % 8 == 0
 
 

@@ -215,7 +215,7 @@ def test_long_launch_equals_split_launches():
     case = CS.CASES["short_servo"]
     prm = PU.case_params(case)
     tape = CS.case_tape(case)[:2500]
-    skip = {"win_vsum", "win_sparks", "win_short_us", "win_steps", "mech_traj", "mech_ckpt"}
+    skip = {"win_vsum", "win_sparks", "win_short_us", "win_steps", "mech_traj", "mech_ckpt", "mech_prog"}
     for injected in (True, False):
         engs = [Engine(4, prm, seed=11, env_id_base=5) for _ in range(2)]
         draws = torch.from_numpy(np.stack([tape] * 4)).to(engs[0].device) if injected else None
