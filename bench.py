@@ -181,9 +181,12 @@ def run_gpu_arm(args):
         raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # stdout carries exactly one JSON line: everything else written to fd 1 during the run (NCCL's
+    # "NCCL version ..." banner comes from C code) is sent to stderr; the line itself goes to the saved fd
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        # stdout carries exactly one JSON line: NCCL's own banner ("NCCL version ...") goes to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
 
     E = args.envs_per_gpu
@@ -380,7 +383,8 @@ def run_gpu_arm(args):
         if not args.no_cpu_baseline and world == 1:
             cb, _, _ = cpu_oracle_throughput(args.cpu_baseline_seconds)
             out["cpu_baseline"] = cb
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -173,6 +173,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     constexpr int WARPS = (W == 1) ? SPARC_BLOCK_THREADS / 32 : W;
     __shared__ float sm_halo[2][W][2];
     __shared__ double sm_red[W];
+    __shared__ uint32_t sm_mech_ready[WARPS];
     __shared__ float sm_log[LOG ? WARPS : 1][LOG ? 32 * (K + 1) : 1];   // field-log staging: coalesced row stores
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
@@ -366,10 +367,13 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     // first blocks one poll covers many blocks (mech_ready caches the last value seen; the poll
     // itself is out of line, mech_wait).
     const double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
-    uint32_t mech_ready = 0;                    // pre-pass blocks known to be published
+    // pre-pass blocks known to be published, per warp, in shared memory (read once per 32-µs block;
+    // a register held across the stencil loops costs more than the LDS)
+    volatile uint32_t *mech_ready = &sm_mech_ready[wib];
+    *mech_ready = 0;
     auto need_mech = [&](int upto_us) {         // positions of launch-µs < upto_us and checkpoints up to there
         const uint32_t need = (uint32_t)((upto_us + SPARC_MECH_CKPT - 1) / SPARC_MECH_CKPT);
-        if (need > mech_ready) mech_ready = mech_wait((const uint32_t *)S.mech_prog + e, a.mech_seq, need);
+        if (need > *mech_ready) *mech_ready = mech_wait((const uint32_t *)S.mech_prog + e, a.mech_seq, need);
     };
     const double wire0 = wire, delta_old0 = target_delta, delta_new0 = (double)a.act.servo[e];
     const int first_latch_it = (next_latch - time > 0) ? next_latch - time : 0;
@@ -637,8 +641,7 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         it += nb;
     }
     if (!done) {                                // end-of-launch mechanics state from the pre-pass
-        need_mech(a.n_us);
-        wire = __ldcg(traj + a.n_us - 1);
+        wire = __ldcg(traj + a.n_us - 1);       // published: the last block of the loop waited for it
         v = __ldcg(S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2);
         prev_accel = __ldcg(S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2 + 1);
     }
