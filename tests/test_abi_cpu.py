@@ -132,3 +132,32 @@ def test_crater_mode_mapping_extension():
     assert doc.crater_mean[13] == ref.crater_mean[5]          # "I13 = 215 A -> 5 A crater data" (run_simulation.py:44)
     with pytest.raises(ValueError):
         P.derive_params(cfg, "position", material=P.MaterialModuleParameters(crater_mode_mapping="nearest"))
+
+
+def test_prepass_handoff_is_in_the_machine_code(native):
+    """The overlap of the mechanics pre-pass with the step kernel rests on three instructions; check
+    the built sm_100a code carries them (no GPU needed): the pre-pass triggers the dependent launch
+    (PREEXIT = griddepcontrol.launch_dependents) and publishes with a GPU-scope release store, the
+    step kernel's poll is a GPU-scope acquire load that also drops L1 (CCTL.IVALL)."""
+    import shutil
+    import subprocess
+
+    cuobjdump = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(cuobjdump):
+        pytest.skip("cuobjdump not available")
+    from sparc_b200 import build
+
+    obj_dir = build.LIB_PATH + ".obj"
+
+    def sass(obj):
+        path = os.path.join(obj_dir, obj)
+        if not os.path.exists(path):
+            pytest.skip(f"{path} not kept by this build")
+        return subprocess.run([cuobjdump, "-sass", path], capture_output=True, text=True, check=True).stdout
+
+    mech = sass("mech_kernel.o")
+    assert "PREEXIT" in mech
+    assert re.search(r"MEMBAR\.\w+\.GPU", mech) and re.search(r"STG\.E\.STRONG\.GPU", mech)
+    step = sass("step_inst_w1.o")
+    poll = step[step.index("mech_wait"):] if "mech_wait" in step else step
+    assert re.search(r"LDG\.E\.STRONG\.GPU", poll) and "CCTL.IVALL" in poll
