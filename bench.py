@@ -173,7 +173,8 @@ def run_gpu_arm(args):
 
     import torch.distributed as dist
     from sparc_b200 import build as sb_build
-    sb_build.build()
+    if not os.environ.get("SPARC_LIB_PATH"):    # an explicitly named library (A/B experiments) is used as it is
+        sb_build.build()
     from sparc_b200 import params as P
     from sparc_b200.engine import Engine, measure_fp32_peak
 
