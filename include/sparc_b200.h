@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SPARC_ABI_VERSION 1
+#define SPARC_ABI_VERSION 2
 #define SPARC_MAX_MODE 19          /* current modes I1..I19, modules/currents.json */
 #define SPARC_N_DRAW_SLOTS 5       /* u1,u2,u3,u4,z5 per µs — see sparc_step_injected */
 #define SPARC_N_STATS 8
@@ -132,6 +132,7 @@ typedef struct SparcActions {
  * one contiguous array per field, temperature field as [n_envs][n_pad] float32.
  * Field table: name, element type ('d' f64, 'f' f32, 'i' i32), byte offset, element count. */
 int sparc_abi_version(void);
+size_t sparc_params_bytes(void);             /* sizeof(SparcParams) of the built library (binding self-check) */
 const char *sparc_last_error(void);
 
 int sparc_num_fields(void);
@@ -150,6 +151,12 @@ int sparc_init(void *state, const SparcParams *p, int n_envs, void *stream);
 /* EDMState() + WireEDMEnv.reset() (wire_edm.py:106-114) + fresh module state for the envs whose
  * mask byte is non-zero (mask == NULL: all).  `episode` increments for reset envs. */
 int sparc_reset(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream);
+
+/* sparc_reset with the episode counter of the reset envs set back to 0: the state a freshly
+ * initialised blob has.  This is `reset(seed=s)` (wire_edm.py:106-107 re-seeds np_random through
+ * gym.Env.reset): the same seed must replay the same episode, so the Philox counter word that
+ * separates successive episodes of one env starts over. */
+int sparc_reseed(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream);
 
 /* n_us reference step() calls for every env, on-device Philox4x32-10 draws keyed by
  * (seed, env_id_base + env, episode, µs).  Envs already terminated are left untouched.

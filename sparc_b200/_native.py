@@ -9,6 +9,7 @@ from .params import SparcParams
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SPARC_LIB_PATH") or os.path.join(HERE, "_lib", "libsparc_b200.so")
 
+ABI_VERSION = 2        # include/sparc_b200.h SPARC_ABI_VERSION this binding was written against
 N_OBS = 8
 N_STATS = 8
 N_DRAW_SLOTS = 5
@@ -35,7 +36,8 @@ _lib = None
 
 # every symbol include/sparc_b200.h declares
 EXPORTS = ("sparc_abi_version", "sparc_last_error", "sparc_num_fields", "sparc_field_info",
-           "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_step",
+           "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_reseed",
+           "sparc_params_bytes", "sparc_step",
            "sparc_step_injected", "sparc_step_logged", "sparc_step_sampled", "sparc_step_observe", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
            "sparc_step_host", "sparc_host_action_pitch", "sparc_launch_info", "sparc_measure_fp32_peak")
 
@@ -61,6 +63,8 @@ def lib():
     L.sparc_padded_segments.argtypes = [i32]
     L.sparc_init.argtypes = [vp, PP, i32, vp]
     L.sparc_reset.argtypes = [vp, PP, i32, vp, vp]
+    L.sparc_reseed.argtypes = [vp, PP, i32, vp, vp]
+    L.sparc_params_bytes.restype = sz
     L.sparc_step.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp]
     L.sparc_step_injected.argtypes = [vp, PP, PA, i32, i32, vp, vp]
     L.sparc_step_logged.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, i32, i32, vp]
@@ -75,6 +79,11 @@ def lib():
     L.sparc_step_host.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, vp]
     L.sparc_measure_fp32_peak.argtypes = [vp, sz, C.POINTER(C.c_double)]
     L.sparc_launch_info.argtypes = [i32, i32, C.POINTER(C.c_int32)]
+    # a stale or foreign library (SPARC_LIB_PATH) must not be fed a SparcParams of another layout
+    if L.sparc_abi_version() != ABI_VERSION or L.sparc_params_bytes() != C.sizeof(SparcParams):
+        raise SparcError(f"{LIB_PATH}: ABI version {L.sparc_abi_version()} / sizeof(SparcParams) "
+                         f"{L.sparc_params_bytes()} do not match this binding ({ABI_VERSION} / "
+                         f"{C.sizeof(SparcParams)}): rebuild with `python -m sparc_b200.build --force`")
     _lib = L
     return L
 

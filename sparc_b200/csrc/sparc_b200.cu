@@ -392,6 +392,13 @@ int sparc_reset(void *state, const SparcParams *p, int n_envs, const uint8_t *ma
     return do_reset(state, p, n_envs, mask_dev, stream, 0);
 }
 
+int sparc_reseed(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream)
+{
+    return do_reset(state, p, n_envs, mask_dev, stream, 1);
+}
+
+size_t sparc_params_bytes(void) { return sizeof(SparcParams); }
+
 int sparc_step(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
                uint64_t seed, uint32_t env_id_base, void *stream)
 {

@@ -76,7 +76,7 @@ class BatchedWireEDMEnv:
         """Fresh-env state for all envs (or the masked ones).  A seed re-keys the Philox streams."""
         if seed is not None:
             self.engine.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
-        self.engine.reset(mask)
+        self.engine.reset(mask, reseed=seed is not None)
         self._arm_latch(mask)
         return self._obs(), {}
 

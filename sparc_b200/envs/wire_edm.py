@@ -77,7 +77,7 @@ class WireEDMEnv(EnvBase):
         if seed is not None:
             self.np_random = np.random.default_rng(seed)
             self._engine.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
-        self._engine.reset(None)
+        self._engine.reset(None, reseed=seed is not None)
         return self._get_obs(), {}
 
     def _stage(self, action):

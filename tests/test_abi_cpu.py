@@ -27,7 +27,8 @@ def test_library_exports_every_declared_symbol(native):
     for sym in sorted(declared):
         assert hasattr(L, sym), f"{sym} declared in include/sparc_b200.h but not exported"
     assert set(native.EXPORTS) == declared
-    assert L.sparc_abi_version() == 1
+    assert L.sparc_abi_version() == native.ABI_VERSION
+    assert L.sparc_params_bytes() == C.sizeof(native.SparcParams)
 
 
 def test_params_struct_size_matches_c(native):

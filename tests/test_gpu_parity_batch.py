@@ -1,0 +1,170 @@
+"""Parity at BASELINE batch sizes, under full occupancy ("next round" item 1).
+
+The step kernel consumes the mechanics pre-pass WHILE it is still running (programmatic dependent
+launch, per-env progress words).  With a handful of envs the producer is always done before the
+consumer's first poll; only thousands of envs over several waves make the two really overlap.  So
+the production path (on-device Philox) is run at 4096 / 8192 / 16384 envs and sampled envs — first
+and last block, one per 148-block stride, a random set — are compared event for event with
+`OracleEnv.run(seed, env_id)`, which implements the same counter-based stream.
+
+Bar: discrete fields exact, fp64 scalars 1e-12, temperature field |dT| <= 2e-3 K + 1e-5 |T|.
+"""
+import hashlib
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import parity_util as PU
+from oracle import cases as CS
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SEED = 0x5EED5EED12345678
+
+
+def sample_envs(n_envs, envs_per_block, n_random=40, key=0):
+    """First/last block, one env from every 148-block stride (alternating the env within the
+    block), plus a seeded random set."""
+    blocks = (n_envs + envs_per_block - 1) // envs_per_block
+    s = {0, min(envs_per_block - 1, n_envs - 1), n_envs - 1, max(n_envs - envs_per_block, 0)}
+    for k, b in enumerate(range(0, blocks, 148)):
+        s.add(min(b * envs_per_block + k % envs_per_block, n_envs - 1))
+    rng = np.random.default_rng(key)
+    s.update(int(x) for x in rng.integers(0, n_envs, n_random))
+    return sorted(s)
+
+
+def compare_with_oracles(eng, oracles, envs, where, T_dev=None):
+    f, i = PU.read_rows(eng, envs=envs)
+    T = eng.T[np.asarray(envs)].cpu().numpy() if T_dev is None else T_dev
+    worst = 0.0
+    for k, e in enumerate(envs):
+        fo, io = oracles[e].record(0)
+        io = io.astype(np.int64)
+        io[-1] = int(io[11] or io[12])
+        PU.assert_rows_match(f[k], i[k], fo, io, where=f"{where} env {e}")
+        ref = oracles[e].temperature
+        err = np.abs(T[k].astype(np.float64) - ref.astype(np.float64))
+        worst = max(worst, float(err.max()))
+        assert np.all(err <= PU.T_ATOL + PU.T_RTOL * np.abs(ref)), f"{where} env {e}: max dT {err.max()}"
+    return worst
+
+
+@pytest.mark.parametrize("n_envs", [4096, 8192, 16384])
+def test_cfg2_philox_at_baseline_batch_sizes(n_envs):
+    """BASELINE configs[1] at its stated size (and 2x / 4x): 20 control steps, quickstart action."""
+    from sparc_b200.engine import Engine
+
+    case = CS.CASES["cfg2_default"]
+    action = [float(np.float32(x)) for x in case["actions"][0]]
+    base = 7000
+    eng = Engine(n_envs, PU.case_params(case), seed=SEED, env_id_base=base)
+    PU.stage_action(eng, action)
+    info = eng.launch_info()
+    envs = sample_envs(n_envs, max(1, info["block_threads"] // info["lanes_per_env"]), key=n_envs)
+    assert len(envs) >= 64 or n_envs < 8192
+    oracles = {e: O.OracleEnv(**CS.oracle_overrides(case)) for e in envs}
+    worst = 0.0
+    for step in range(20):
+        eng.step(1000)
+        for e in envs:
+            oracles[e].run(1000, [action], draws=None, seed=SEED, env_id=base + e, rec_every=0)
+        if step % 5 == 4 or step == 0:
+            worst = max(worst, compare_with_oracles(eng, oracles, envs, f"cfg2 x{n_envs} step {step}"))
+    assert int(eng["stat_sparks"].sum().item()) > 0
+    print(f"\n[cfg2 x{n_envs}] {len(envs)} sampled envs match the oracle over 20 control steps; max |dT| {worst:.3e} K")
+
+
+def test_cfg3_closed_loop_philox_16384_envs():
+    """BASELINE configs[2]: 16384 envs, position mode, P gap controller (25 um, limit 1) closed on the
+    device; every sampled oracle is driven by the reference's controller arithmetic
+    (experiments/run_simulation.py:27-39) from its own state."""
+    from sparc_b200 import BatchedWireEDMEnv, EnvironmentConfig, GapController
+
+    E, STEPS, SI, base = 16384, 20, 1000, 300000
+    gen = dict(target_voltage=80.0, current_mode=5, ON_time=3.0, OFF_time=80.0)
+    ctrl = GapController(25.0, "position", limit=1.0, generator=gen)
+    env = BatchedWireEDMEnv(E, config=EnvironmentConfig(**CS.README_CFG), mechanics_control_mode="position",
+                            seed=SEED, env_id_base=base, latch_first_action=False)
+    env.reset(seed=SEED)            # a seeded reset starts the episode counter over: episode 0, like the oracle
+    info = env.engine.launch_info()
+    envs = sample_envs(E, max(1, info["block_threads"] // info["lanes_per_env"]), key=3)
+    case = {"config": CS.README_CFG, "mode": "position"}
+    oracles = {e: O.OracleEnv(**CS.oracle_overrides(case)) for e in envs}
+    worst = 0.0
+    for k in range(STEPS):
+        env.step(ctrl(env))
+        for e in envs:
+            f, _ = oracles[e].record()
+            servo = np.float32(np.clip((f[0] - f[1] - 25.0) * 0.1, -1.0, 1.0))
+            oracles[e].run(SI, [[float(servo), 80.0, 5, 3.0, 80.0]], draws=None, seed=SEED, env_id=base + e, rec_every=0)
+        if k % 5 == 4 or k == 0:
+            worst = max(worst, compare_with_oracles(env.engine, oracles, envs, f"cfg3 step {k}"))
+    assert float(env.state_tensor("stat_sparks").sum()) > 0
+    print(f"\n[cfg3 x{E}] {len(envs)} sampled envs match the oracle over {STEPS} closed-loop control steps; "
+          f"max |dT| {worst:.3e} K")
+
+
+def test_thick_wire_block_per_env_1024_envs():
+    """One W > 1 case at size: N = 2200 (block per env, shared-memory halos), 1024 envs, I13 ON 3 / OFF 30."""
+    from sparc_b200.engine import Engine
+
+    case = CS.CASES["thick_2200"]
+    action = [float(np.float32(x)) for x in case["actions"][0]]
+    n_envs, base = 1024, 50
+    eng = Engine(n_envs, PU.case_params(case), seed=SEED, env_id_base=base)
+    PU.stage_action(eng, action)
+    assert eng.launch_info()["lanes_per_env"] > 32
+    envs = sample_envs(n_envs, 1, n_random=20, key=11)
+    oracles = {e: O.OracleEnv(**CS.oracle_overrides(case)) for e in envs}
+    worst = 0.0
+    for step in range(8):
+        eng.step(1000)
+        for e in envs:
+            oracles[e].run(1000, [action], draws=None, seed=SEED, env_id=base + e, rec_every=0)
+        if step % 4 == 3:
+            worst = max(worst, compare_with_oracles(eng, oracles, envs, f"thick_2200 x{n_envs} step {step}"))
+    print(f"\n[thick_2200 x{n_envs}] {len(envs)} sampled envs match; max |dT| {worst:.3e} K")
+
+
+_HASH_SCRIPT = r"""
+import hashlib, sys
+import numpy as np
+sys.path.insert(0, {root!r}); sys.path.insert(0, {tests!r})
+import parity_util as PU
+from oracle import cases as CS
+from sparc_b200.engine import Engine
+case = CS.CASES["cfg2_default"]
+eng = Engine(4096, PU.case_params(case), seed={seed}, env_id_base=0)
+PU.stage_action(eng, [float(np.float32(x)) for x in case["actions"][0]])
+for _ in range(6):
+    eng.step(1000)
+h = hashlib.sha256()
+for name in ("wp", "wire", "v", "prev_accel", "debris_volume", "time", "spark_state", "spark_dur", "flags", "stat_sparks", "T"):
+    h.update(eng[name].cpu().numpy().tobytes())
+print("STATEHASH", h.hexdigest())
+"""
+
+
+def _state_hash(extra_env):
+    env = dict(os.environ)
+    env.update(extra_env)
+    code = _HASH_SCRIPT.format(root=ROOT, tests=os.path.join(ROOT, "tests"), seed=SEED)
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = [l for l in out.stdout.splitlines() if l.startswith("STATEHASH")]
+    assert line, out.stdout[-2000:]
+    return line[-1].split()[1]
+
+
+def test_overlapped_and_serial_prepass_agree_bit_for_bit():
+    """SPARC_NO_PDL=1 runs the mechanics pre-pass and the step kernel in plain stream order; the
+    overlapped hand-off must produce the same bytes in every state field at 4096 envs."""
+    a = _state_hash({})
+    b = _state_hash({"SPARC_NO_PDL": "1"})
+    assert a == b
