@@ -32,11 +32,11 @@
 extern "C" {
 #endif
 
-#define SPARC_ABI_VERSION 2
+#define SPARC_ABI_VERSION 4
 #define SPARC_MAX_MODE 19          /* current modes I1..I19, modules/currents.json */
 #define SPARC_N_DRAW_SLOTS 5       /* u1,u2,u3,u4,z5 per µs — see sparc_step_injected */
 #define SPARC_N_STATS 8
-#define SPARC_N_OBS 8
+#define SPARC_N_OBS 12
 
 /* rows of the per-signal log (sparc_step_sampled); names are the reference's EDMState attributes */
 enum {
@@ -73,7 +73,9 @@ enum {
     SPARC_F_TARGET = 4,         /* EDMState.is_target_distance_reached */
     SPARC_F_MODE_ERROR = 8,     /* crater table miss: the reference raises ValueError, material.py:108-113 */
     SPARC_F_HAS_Y = 16,         /* spark_status[1] is not None */
-    SPARC_F_THERMAL_BREAK = 32  /* break came from WireModule._check_wire_breaking (early return, wire_edm.py:129-130) */
+    SPARC_F_THERMAL_BREAK = 32, /* break came from WireModule._check_wire_breaking (early return, wire_edm.py:129-130) */
+    SPARC_F_HANDOFF_SLOW = 64   /* diagnostic, not an error: the mechanics pre-pass of some launch did not publish in time
+                                   and the step kernel computed this env's trajectory itself (same values) */
 };
 #define SPARC_F_DONE (SPARC_F_BROKEN | SPARC_F_TARGET | SPARC_F_MODE_ERROR)
 
@@ -112,6 +114,9 @@ typedef struct SparcParams {
         temp_update_factor, density_times_cp, plasma_efficiency, base_convection_coefficient,
         convection_velocity_factor, convection_flow_enhancement;
     float critical_temperature_f32, breaking_temperature_f32;
+    /* (float)(temp_update_factor * k_cond_coeff): the conduction coefficient of the stencil, a launch constant
+     * the kernel reads straight from the parameter bank (uniform-register operand) */
+    float cond_coeff_f32, reserved1;
     /* mechanics (mechanics.py:48-57) */
     double mech_dt, damping_coeff, stiffness_coeff, omega_n, max_acceleration, max_jerk_dt,
         max_speed;
@@ -201,7 +206,10 @@ int sparc_step_observe(void *state, const SparcParams *p, const SparcActions *ac
 
 /* Observation summary of the last step call, obs_dev[SPARC_N_OBS][n_envs] float32:
  * 0 gap [µm], 1 wire_velocity [µm/s], 2 mean voltage over the call [V], 3 sparks ignited in the
- * call, 4 short-circuit µs in the call, 5 max wire temperature [K], 6 debris_density, 7 flags. */
+ * call, 4 short-circuit µs in the call, 5 max wire temperature [K], 6 debris_density, 7 flags;
+ * rows 8..10 carry int32 BIT PATTERNS (read them through an int32 view): 8 time [µs], 9 spark_status[0],
+ * 10 time_since_servo — with flags, everything the reference's `info` dict and the control-step test
+ * of `WireEDMEnv.step` need (wire_edm.py:117,150-156) without a second read-back; 11 reserved (0). */
 int sparc_observe(const void *state, int n_envs, int n_segments, float *obs_dev, void *stream);
 
 /* Sum over envs of [sparks, short µs, short events, crater µm³, short pulses, env-µs simulated,

@@ -9,8 +9,8 @@ from .params import SparcParams
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SPARC_LIB_PATH") or os.path.join(HERE, "_lib", "libsparc_b200.so")
 
-ABI_VERSION = 2        # include/sparc_b200.h SPARC_ABI_VERSION this binding was written against
-N_OBS = 8
+ABI_VERSION = 4        # include/sparc_b200.h SPARC_ABI_VERSION this binding was written against
+N_OBS = 12         # rows 0..7 float32; rows 8..10 int32 bit patterns (time, spark_state, time_since_servo)
 N_STATS = 8
 N_DRAW_SLOTS = 5
 # rows of the per-signal log (include/sparc_b200.h SPARC_SIG_*), by the reference's EDMState names

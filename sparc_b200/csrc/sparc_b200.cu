@@ -58,6 +58,7 @@ constexpr int kNumFields = (int)(sizeof(kFields) / sizeof(kFields[0]));
 constexpr int kFieldT = kNumFields - 4, kFieldTraj = kNumFields - 3, kFieldCkpt = kNumFields - 2;
 
 constexpr size_t kAlign = 256;
+constexpr int SPARC_SELF_MECH_US = 8;
 
 int padded_segments(int n_segments) { return (int)sparc_align_up((size_t)n_segments, 32); }
 
@@ -140,6 +141,10 @@ __global__ void observe_kernel(SparcStatePtrs S, int n_envs, int n_segments, flo
         obs[5 * (size_t)n_envs + e] = m;
         obs[6 * (size_t)n_envs + e] = (float)S.debris_density[e];
         obs[7 * (size_t)n_envs + e] = (float)S.flags[e];
+        obs[8 * (size_t)n_envs + e] = __int_as_float(S.time[e]);
+        obs[9 * (size_t)n_envs + e] = __int_as_float(S.spark_state[e]);
+        obs[10 * (size_t)n_envs + e] = __int_as_float(S.t_servo[e]);
+        obs[11 * (size_t)n_envs + e] = 0.0f;
     }
 }
 
@@ -220,10 +225,62 @@ __global__ void fma_peak_kernel(float *out, float a, float b, int iters)
 // ---- step kernel dispatch -------------------------------------------------------------------
 using Variant = sparc::StepVariant;
 
-// fewest warps per env, then fewest cells per lane, whose 32*W*K slots hold the n_segments-1 dynamic cells
-const Variant *pick_variant(int n_segments)
+// Region layout of the wire in the 64*W halves of an environment's lanes (SparcLayout, step_common.cuh).
+// A region of n cells takes nh >= ceil(n/H) halves, nh*H - n of them short (one pad each).
+// ALIGNED (three regions: below the zone, the zone, above it; per-half coefficients): pads only in y
+// halves (odd h) and the wire ends on a y half, so the stencil needs no x-side pad handling.
+// Otherwise: ONE region, the first p halves short, per-cell coefficients (the general kernel variant).
+int odd_halves(int hb, int nh) { return (hb + nh) / 2 - hb / 2; }    // odd h in [hb, hb + nh)
+
+bool try_aligned(const int n[3], const int nh[3], int H, int NH, sparc::SparcLayout *L, const int cb[3])
 {
-    const int M = n_segments - 1;
+    int hb = 0;
+    L->hb[0] = 0;
+    for (int r = 0; r < 3; r++) {
+        const int p = nh[r] * H - n[r];
+        if (p < 0 || p > odd_halves(hb, nh[r])) return false;
+        L->p[r] = p;
+        L->cb[r] = cb[r];
+        hb += nh[r];
+        L->hb[r + 1] = hb;
+    }
+    return hb <= NH && hb % 2 == 0;
+}
+
+bool compute_layout(const SparcParams *p, int K, int W, sparc::SparcLayout *L)
+{
+    const int H = K / 2, NH = 64 * W, N = p->n_segments;
+    int zs = p->actual_zone_start, ze = p->actual_zone_end;
+    if (!(ze > zs)) { zs = 1; ze = 1; }          // empty zone
+    zs = zs < 1 ? 1 : (zs > N ? N : zs);
+    ze = ze < zs ? zs : (ze > N ? N : ze);
+    const int cb[4] = {1, zs, ze, N};
+    int n[3], nh[3];
+    for (int r = 0; r < 3; r++) { n[r] = cb[r + 1] - cb[r]; nh[r] = (n[r] + H - 1) / H; }
+    L->aligned = 1;
+    if (try_aligned(n, nh, H, NH, L, cb)) return true;
+    for (int r = 2; r >= 0; r--) {               // one more half in one region: fixes an odd total or too few y halves
+        if (n[r] == 0) continue;
+        int nh2[3] = {nh[0], nh[1], nh[2]};
+        nh2[r] += 1;
+        if (try_aligned(n, nh2, H, NH, L, cb)) return true;
+    }
+    // general layout
+    const int M = N - 1;
+    int nh0 = (M + H - 1) / H, p0 = nh0 * H - M;
+    if (p0 > nh0 || nh0 > NH) return false;
+    L->aligned = 0;
+    L->hb[0] = 0; L->hb[1] = L->hb[2] = L->hb[3] = nh0;
+    L->p[0] = p0; L->p[1] = L->p[2] = 0;
+    L->cb[0] = 1; L->cb[1] = L->cb[2] = N;
+    return true;
+}
+
+// fewest warps per env, then fewest cells per lane, whose 32*W*K slots hold the n_segments-1 dynamic
+// cells in a valid layout (aligned if the slack allows, else one region with per-cell coefficients)
+const Variant *pick_variant(const SparcParams *p, sparc::SparcLayout *L_out)
+{
+    const int M = p->n_segments - 1;
     const Variant *(*tables[4])(int *) = {sparc::step_variants_w1, sparc::step_variants_w2, sparc::step_variants_w4,
                                           sparc::step_variants_w8};
     const Variant *best = nullptr;
@@ -233,12 +290,17 @@ const Variant *pick_variant(int n_segments)
         for (int i = 0; i < n; i++) {
             const Variant &v = tab[i];
             if (v.K * 32 * v.W < M) continue;
-            if (!best || v.W < best->W || (v.W == best->W && v.K < best->K)) best = &v;
+            if (best && !(v.W < best->W || (v.W == best->W && v.K < best->K))) continue;
+            sparc::SparcLayout L;
+            if (!compute_layout(p, v.K, v.W, &L)) continue;
+            best = &v;
+            if (L_out) *L_out = L;
         }
     }
     return best;
 }
 
+// Grid of the step kernel: one warp (W == 1) or block (W > 1) per environment.
 void launch_geometry(const Variant *v, int n_envs, int *blocks, int *threads)
 {
     if (v->W == 1) {
@@ -281,9 +343,11 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
         return fail(SPARC_E_INVALID, "null action array");
     if (n_us < 0) return fail(SPARC_E_INVALID, "n_us must be >= 0");
     if (n_us == 0) return SPARC_OK;
-    const Variant *v = pick_variant(p->n_segments);
+    sparc::SparcLayout lay;
+    const Variant *v = pick_variant(p, &lay);
     if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6145 wire segments)");
     SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
+    const sparc::StepFn fn = v->fn[tlog ? 1 : 0][draws ? 1 : 0][lay.aligned ? 1 : 0];
     int blocks, threads;
     launch_geometry(v, n_envs, &blocks, &threads);
     // one (mechanics pre-pass, fused step) pair per chunk: at most SPARC_MECH_EPOCH µs, cut at every
@@ -313,8 +377,12 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
         // serialization) starts as soon as every pre-pass block is resident, and consumes the
         // trajectory block by block behind per-env progress tags (mech_prog) instead of waiting
         // for the pre-pass grid to drain.
-        a.mech_seq = next_mech_seq();
-        sparc::mech_launch(*p, S, a, (cudaStream_t)stream);
+        // Launches of at most SPARC_SELF_MECH_US µs (the drop-in's 1-µs step(), per-µs sampling) skip the
+        // pre-pass kernel: mech_seq = 0 tells the step kernel to evaluate the few mechanics steps itself.
+        const bool prepass = n > SPARC_SELF_MECH_US;
+        a.mech_seq = prepass ? next_mech_seq() : 0u;
+        a.lay = lay;
+        if (prepass) sparc::mech_launch(*p, S, a, (cudaStream_t)stream);
         {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3((unsigned)blocks);
@@ -327,8 +395,8 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
             cfg.attrs = attr;
             // SPARC_NO_PDL=1 (diagnostics): plain stream order, the step kernel starts after the pre-pass
             static const bool no_pdl = getenv("SPARC_NO_PDL") != nullptr;
-            cfg.numAttrs = no_pdl ? 0 : 1;
-            CUDA_TRY(cudaLaunchKernelEx(&cfg, v->fn[tlog ? 1 : 0][draws ? 1 : 0], *p, S, a));
+            cfg.numAttrs = (no_pdl || !prepass) ? 0 : 1;
+            CUDA_TRY(cudaLaunchKernelEx(&cfg, fn, *p, S, a));
         }
         t += n;
         if (signals && t % sample_every == 0) {
@@ -556,7 +624,10 @@ int sparc_measure_fp32_peak(void *scratch_dev, size_t scratch_bytes, double *tfl
 int sparc_launch_info(int n_envs, int n_segments, int32_t out[4])
 {
     if (!out || n_envs <= 0 || n_segments < 2) return fail(SPARC_E_INVALID, "bad launch_info arguments");
-    const Variant *v = pick_variant(n_segments);
+    SparcParams q;                               // geometry only: no zone (the kernel variant does not depend on it
+    memset(&q, 0, sizeof(q));                    // except through K when the aligned layout needs more slack)
+    q.n_segments = n_segments;
+    const Variant *v = pick_variant(&q, nullptr);
     if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6145 wire segments)");
     int blocks, threads;
     launch_geometry(v, n_envs, &blocks, &threads);

@@ -80,6 +80,24 @@ __device__ __forceinline__ uint32_t pick4(const uint32_t w[4], int idx)
 
 namespace sparc {
 
+// Register layout of the wire inside one environment's 32*W lanes (computed on the host per launch,
+// sparc_b200.cu:compute_layout).  Every lane holds two HALVES of H = K/2 slots (the x and the y
+// components of its packed registers); half h = 2*lane + {0,1} covers consecutive cells.  The cells
+// 1..N-1 are split into up to three REGIONS (below the flushing zone, the zone, above it; WireModule
+// gives the zone its own convection coefficient, wire.py:349-374) and every region starts on a half
+// boundary, so the two convection coefficients are one value per half instead of one per cell.
+// The slack is absorbed by SHORT halves: a short half holds H-1 cells and a pad in its last slot (a
+// compile-time register), which the stencil keeps equal to the right-hand neighbour, so that it is
+// transparent.  The first p[r] halves of region r are short.  Halves >= hb[3] hold no cells; the last
+// real cell of half hb[3]-1 is cell N-1, the zero-flux end (wire.py:95).  aligned == 0: one region,
+// per-cell coefficients (geometries whose regions are too small to be aligned).
+struct SparcLayout {
+    int hb[4];      // first half of region r; hb[3] = number of halves in use
+    int p[3];       // short halves of region r
+    int cb[3];      // first cell of region r
+    int aligned;
+};
+
 // Everything the kernel needs besides the state pointers.
 struct StepArgs {
     SparcActions act;        // device pointers
@@ -92,10 +110,11 @@ struct StepArgs {
     int it_base, total_us;   // this launch covers µs [it_base, it_base + n_us) of a call of total_us µs
     float *obs;              // observation summary [SPARC_N_OBS][n_envs] written by the kernel epilogue, or NULL
     uint32_t mech_seq;       // tag of this launch pair in SparcStatePtrs::mech_prog (multiple of 64)
+    SparcLayout lay;
 };
 
 #ifndef SPARC_BLOCK_THREADS
-#define SPARC_BLOCK_THREADS 64      /* W == 1: two envs per block; 7 blocks/SM = 14 warps/SM divides 4096 and 8192 envs into full waves */
+#define SPARC_BLOCK_THREADS 64      /* W == 1: two envs per block */
 #endif
 
 // Sigmoid exponent above which the debris-short probability 1/(1+e^x) < 4.3e-18 can be treated
@@ -133,6 +152,27 @@ struct EnvState {
     int e, it;
     uint32_t env_id, episode;
     bool writer;
+    // ---- launch bookkeeping (registers in the round-1 kernel; the record lives in shared memory) ----
+    double wire0, delta_old0, delta_new0;        // mechanics inputs of this launch (for the exact rewind)
+    double fin_wire, fin_v, fin_pa;              // mechanics state to store at the end of the launch
+    double lam_bound;                            // upper bound of lambda(gap) over all gaps
+    double cfac;                                 // f = temp_update_factor
+    int crit_count, w_zone_counter, next_latch, skip_flush, tsi_break, time0, first_latch_it;
+    int win_short0, win_steps0, win_steps_out;
+    uint32_t w_thresh;                           // Philox word >= w_thresh can never ignite
+    uint32_t rng_cbase;                          // first Philox counter of the cached window
+    uint32_t mech_ready;                         // pre-pass blocks known to be published
+    uint32_t mech_self;                          // blocks this warp computed itself after a hand-off timeout
+    bool ran_fast, zone_mean_written, cold_ok, convex, rng_valid, done;
+};
+
+// Per-warp record in shared memory: the scalar state, the wire positions of the current 32-µs block
+// (pos[0] before its first µs, pos[1 + l] after µs l) and a window of Philox ignition words
+// (rng[c - rng_cbase][w] = word w of counter c: 128 µs per refill instead of 32).
+struct __align__(16) WarpRec {
+    uint32_t rng[32][4];
+    double pos[33];
+    EnvState s;
 };
 
 // generator settings as the ignition module sees them (ignition.py:329-343, 98-113): `x or

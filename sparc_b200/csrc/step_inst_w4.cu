@@ -4,7 +4,11 @@
 
 namespace sparc {
 static const StepVariant kTable[] = {
+#ifdef SPARC_QUICK   /* experiments: one variant per W, compiles in seconds */
+    SPARC_STEP_VARIANT(16, 4),
+#else
     SPARC_STEP_VARIANT(16, 4), SPARC_STEP_VARIANT(20, 4), SPARC_STEP_VARIANT(24, 4),
+#endif
 };
 const StepVariant *step_variants_w4(int *n)
 {

@@ -1,22 +1,26 @@
-// step_kernel.cuh — the fused step kernel, "look-ahead" organisation (sm_100a).
+// step_kernel.cuh — the fused step kernel (sm_100a), round-2 organisation.
 //
-// Same mapping as step_kernel.cuh (one warp per environment, the wire temperature field in
-// registers, K cells per lane, halos by warp shuffle) and the same general µs (general_pre), but
-// the per-µs scalar state machines no longer run on every µs:
+// One warp per environment (W == 1; W warps of one block for wires longer than one warp), the wire
+// temperature field in REGISTERS, halos by warp shuffle, the per-µs scalar state machines replaced
+// by a lane-parallel LOOK-AHEAD exactly as in round 1 (mechanics from the pre-pass kernel, quiet-run
+// detection by ballot, scalar-free stencil runs, exact general µs for everything else).  What is new:
 //
-//   * MECHANICS (mechanics.py:79-114) depends on nothing but the latched servo command, so it is
-//     advanced one BLOCK of <= 32 µs ahead of everything else (exact sequential fp64, identical
-//     operations); the 32 wire positions go to shared memory and from there one per lane.
-//   * LOOK-AHEAD: lane l then evaluates, for µs l of the block, every condition under which the
-//     reference's step() is "quiet" (idle/rest, no latch, no short circuit, no ignition, no
-//     hysteresis refresh, no collision, no zone-mean sample).  The ignition roll is evaluated
-//     here too: lane l computes the Philox word of its own µs.  One ballot gives the length n of
-//     the quiet run.
-//   * QUIET RUN: n µs of pure stencil — no scalar instruction in the loop.  When the wire is
-//     provably cold (max T < critical-1 K and the update is a convex combination, so the maximum
-//     cannot grow without a heat source) even the max/break test is skipped.
-//   * everything else takes the exact general µs (general_pre + heated stencil + break test +
-//     termination), one µs at a time.
+//   * REGISTER BUDGET.  Everything that is not the field lives in ONE shared-memory record per warp
+//     (WarpRec: the EnvState the general µs works on, the launch bookkeeping, the 32 wire positions
+//     of the current look-ahead block, a window of Philox words).  Across the stencil loops a lane
+//     holds the field (K floats), FOUR convection coefficients, two conduction scalars and a loop
+//     count — the round-1 kernel held 36 coefficient registers and ~40 scalars and sat at 128
+//     registers with spills; this one fits the 72 that 28 resident warps per SM allow, which is what
+//     4096 envs need to run as ONE wave (6.9 warps per scheduler) instead of two.
+//   * REGION LAYOUT (SparcLayout, step_common.cuh).  Zone boundaries, the zero-flux end and the pad
+//     slots used to be per-cell coefficient registers (cE, c0, cR per cell).  Now the cells are laid out
+//     so that every such boundary falls between two HALVES of a lane: the conduction coefficient is one
+//     scalar for the whole wire, the convection pair one value per half, the zero-flux end is a halo
+//     override, and pads sit in compile-time slots that mirror their right-hand neighbour.  Element by
+//     element the operation sequence on real cells is unchanged (q = fma(cE,T,c0); q = fma(cR,dnext,q);
+//     q = fma(ncL,dprev,q); T += q), so the field is bit-identical to round 1's.
+//   * Philox ignition words are computed for 128 µs at a time (each lane one counter, all four
+//     words kept) instead of 32.
 //
 // Every shortcut is conservative: a µs that is not provably quiet runs the general path, which is
 // the reference's logic statement by statement, so results do not depend on where the run boundaries fall.
@@ -25,22 +29,15 @@
 
 namespace sparc {
 
-// ---- packed stencil ---------------------------------------------------------------------------
-// sm_100 has two-wide fp32 instructions (FFMA2/FADD2, PTX fma.rn.f32x2): one issue slot and one
-// pipe pass for two IEEE-rn operations — measured 1.95 FFMA2 vs 2.1 register-operand FFMA per
-// clock per SM (tools/microbench2.cu).  Lane cells are split in two halves of H = K/2 cells;
-// pair j holds (T[j], T[j+H]) so that neighbour differences of pair j are pair j+1 minus pair j.
-// Element-wise the operation sequence is unchanged: q = fma(cE,T,c0); q = fma(cR,dnext,q);
-// q = fma(ncL,dprev,q); T = T + q.
 __device__ __forceinline__ float2 sub2(const float2 a, const float2 b)
 {
     return __fadd2_rn(a, make_float2(-b.x, -b.y));
 }
 
 // ---- wires longer than one warp: W warps (one thread block) per environment -------------------
-// Each warp runs the scalar state machine redundantly (same inputs, same results, so control flow
-// is identical in all warps of the block); only three things cross warps: the stencil halos
-// (shared memory, double buffered, one barrier per µs), the temperature votes
+// Each warp runs the scalar state machine redundantly on its own record (same inputs, same results,
+// so control flow is identical in all warps of the block); only three things cross warps: the
+// stencil halos (shared memory, double buffered, one barrier per µs), the temperature votes
 // (__syncthreads_or) and the zone-mean sum.
 template <int W>
 struct EnvCtx {
@@ -49,24 +46,46 @@ struct EnvCtx {
     int parity;
 };
 
-template <int W>
-__device__ __forceinline__ void stencil_halos(EnvCtx<W> &c, const float t_first, const float t_last, float &left,
-                                              float &right, const float spoolf)
+// Where the two halves of this lane sit on the wire (SparcLayout).
+struct LaneGeom {
+    int cx0, nx, cy0, ny;   // first cell and number of real cells of the x / y half (n == 0: empty)
+    int rx, ry;             // region of each half (-1: empty)
+};
+
+__device__ __forceinline__ void half_geom(const SparcLayout &L, const int h, const int H, int &c_first, int &n, int &region)
 {
-    constexpr unsigned FULL = 0xffffffffu;
-    left = __shfl_up_sync(FULL, t_last, 1);
-    right = __shfl_down_sync(FULL, t_first, 1);
-    if constexpr (W > 1) {
-        float(*h)[2] = c.halo[c.parity];
-        if (c.lane == 0) h[c.wid][0] = t_first;
-        if (c.lane == 31) h[c.wid][1] = t_last;
-        __syncthreads();
-        if (c.lane == 0 && c.wid > 0) left = h[c.wid - 1][1];
-        if (c.lane == 31 && c.wid < W - 1) right = h[c.wid + 1][0];
-        c.parity ^= 1;
+    if (h >= L.hb[3]) { c_first = 0; n = 0; region = -1; return; }
+    const int r = (h >= L.hb[2]) ? 2 : ((h >= L.hb[1]) ? 1 : 0);
+    const int k = h - L.hb[r], p = L.p[r];
+    int before, sh;
+    if (L.aligned) {                            // pads only in y halves: the first p odd halves of the region
+        const int cnt = (L.hb[r] & 1) ? ((k + 1) >> 1) : (k >> 1);      // odd halves of the region before h
+        before = (cnt < p) ? cnt : p;
+        sh = ((h & 1) && cnt < p) ? 1 : 0;
+    } else {                                    // the first p halves of the (single) region
+        before = (k < p) ? k : p;
+        sh = (k < p) ? 1 : 0;
     }
-    if (c.gl == 0) left = spoolf;
+    c_first = L.cb[r] + k * H - before;
+    n = H - sh;
+    region = r;
 }
+
+__device__ __forceinline__ LaneGeom lane_geom(const SparcLayout &L, const int gl, const int H)
+{
+    LaneGeom g;
+    half_geom(L, 2 * gl, H, g.cx0, g.nx, g.rx);
+    half_geom(L, 2 * gl + 1, H, g.cy0, g.ny, g.ry);
+    return g;
+}
+
+// loop-invariant lane predicates of the stencil
+struct LaneFlags {
+    bool first;             // lane 0 of the env: left neighbour is the spool cell
+    bool short_x, short_y;  // the last slot of the half is a pad
+    bool end_x, end_y;      // the half ends with cell N-1 (zero flux to the right)
+    bool empty_x, empty_y;  // the half holds no cells
+};
 
 template <int W>
 __device__ __forceinline__ bool vote_any(const bool pred)
@@ -75,81 +94,160 @@ __device__ __forceinline__ bool vote_any(const bool pred)
     else return __any_sync(0xffffffffu, pred);
 }
 
-// n quiet µs of compute_thermal_update (wire.py:58-123) without heat sources.  HOT additionally
-// runs _check_wire_breaking (wire.py:376-388) every µs and returns the number of µs executed
-// (n, or j+1 when the wire broke on µs j; `broke` says which).
-template <int H, bool HOT, int W, bool LOG, class LogTick>
-__device__ __forceinline__ int run_quiet(float2 (&T)[H], const float2 (&cE)[H], const float2 (&c0)[H],
-                                         const float2 (&cR)[H], const float ncL, const float spoolf, EnvCtx<W> &ctx,
-                                         const int n, const float crit_T, const float break_T, int &crit_count,
-                                         bool &broke, bool &cold_after, LogTick &&log_tick)
+// Halo exchange and pad upkeep of one µs.  Out: `left` (cell before the x half), `right` (cell after
+// the y half, or the end cell itself at the zero-flux end), `xl` (last real cell of the x half), `yv`
+// (cell after the x half).  Pads are set to their right-hand neighbour, so the packed difference
+// T[H-1] - T[H-2] of a short half is the real cell's difference to its true neighbour.
+template <int H, int W, bool XP>
+__device__ __forceinline__ void stencil_edges(EnvCtx<W> &c, float2 (&T)[H], const LaneFlags &f, const float spoolf,
+                                              float &left, float &right, float &xl, float &yv)
 {
-    const float2 ncL2 = make_float2(ncL, ncL);
+    constexpr unsigned FULL = 0xffffffffu;
+    const float t_last = f.short_y ? T[H - 2].y : T[H - 1].y;
+    left = __shfl_up_sync(FULL, t_last, 1);
+    right = __shfl_down_sync(FULL, T[0].x, 1);
+    if constexpr (W > 1) {
+        float(*h)[2] = c.halo[c.parity];
+        if (c.lane == 0) h[c.wid][0] = T[0].x;
+        if (c.lane == 31) h[c.wid][1] = t_last;
+        __syncthreads();
+        if (c.lane == 0 && c.wid > 0) left = h[c.wid - 1][1];
+        if (c.lane == 31 && c.wid < W - 1) right = h[c.wid + 1][0];
+        c.parity ^= 1;
+    }
+    if (f.first) left = spoolf;
+    if (f.end_y) right = t_last;
+    if (f.short_y) T[H - 1].y = right;
+    if constexpr (XP) {                         // general layout: x halves may be short or hold the end cell
+        xl = f.short_x ? T[H - 2].x : T[H - 1].x;
+        yv = f.end_x ? xl : T[0].y;
+        if (f.short_x) T[H - 1].x = yv;
+    } else {                                    // aligned layout: pads and the end cell sit in y halves only
+        xl = T[H - 1].x;
+        yv = T[0].y;
+    }
+}
+
+// Convection coefficients: one (cE, c0) pair per half when the layout is aligned, per cell otherwise.
+template <int H, bool ALIGNED>
+struct Coefs {
+    float2 cE[ALIGNED ? 1 : H], c0[ALIGNED ? 1 : H];
+    __device__ __forceinline__ float2 e(const int j) const { return cE[ALIGNED ? 0 : j]; }
+    __device__ __forceinline__ float2 z(const int j) const { return c0[ALIGNED ? 0 : j]; }
+};
+
+// maximum over the REAL cells of this lane (pads and empty halves excluded), never below `floor`
+template <int H>
+__device__ __forceinline__ float lane_max(const float2 (&T)[H], const LaneFlags &f, const float floor_v)
+{
+    float mx = floor_v, my = floor_v;
+#pragma unroll
+    for (int j = 0; j < H - 1; j++) { mx = fmaxf(mx, T[j].x); my = fmaxf(my, T[j].y); }
+    mx = f.short_x ? mx : fmaxf(mx, T[H - 1].x);
+    my = f.short_y ? my : fmaxf(my, T[H - 1].y);
+    mx = f.empty_x ? floor_v : mx;
+    my = f.empty_y ? floor_v : my;
+    return fmaxf(mx, my);
+}
+
+// One µs of compute_thermal_update (wire.py:58-123) without heat sources: the halo-independent pairs
+// first so the shuffles complete underneath them (measured +2 % in round 1).
+template <int H, bool ALIGNED, int W>
+__device__ __forceinline__ void stencil_quiet_us(float2 (&T)[H], const Coefs<H, ALIGNED> &co, const float2 cR2,
+                                                 const float2 ncL2, const float spoolf, const LaneFlags &f, EnvCtx<W> &ctx)
+{
+    float left, right, xl, yv;
+    stencil_edges<H, W, !ALIGNED>(ctx, T, f, spoolf, left, right, xl, yv);
+    const float d_mid = yv - xl;
+    const float2 d0 = sub2(T[1], T[0]);         // dnext of pair 0, dprev of pair 1 (old values)
+    float2 dprev = d0;
+#pragma unroll
+    for (int j = 1; j < H - 1; j++) {
+        const float2 dnext = sub2(T[j + 1], T[j]);
+        float2 q = __ffma2_rn(co.e(j), T[j], co.z(j));
+        q = __ffma2_rn(cR2, dnext, q);
+        q = __ffma2_rn(ncL2, dprev, q);
+        dprev = dnext;
+        T[j] = __fadd2_rn(T[j], q);
+    }
+    {
+        const float2 dlast = make_float2(d_mid, right - T[H - 1].y);
+        float2 q = __ffma2_rn(co.e(H - 1), T[H - 1], co.z(H - 1));
+        q = __ffma2_rn(cR2, dlast, q);
+        q = __ffma2_rn(ncL2, dprev, q);
+        T[H - 1] = __fadd2_rn(T[H - 1], q);
+    }
+    {
+        const float2 dfirst = make_float2(T[0].x - left, d_mid);
+        float2 q = __ffma2_rn(co.e(0), T[0], co.z(0));
+        q = __ffma2_rn(cR2, d0, q);
+        q = __ffma2_rn(ncL2, dfirst, q);
+        T[0] = __fadd2_rn(T[0], q);
+    }
+}
+
+// n quiet µs.  HOT additionally runs _check_wire_breaking (wire.py:376-388) every µs and returns the
+// number of µs executed (n, or k+1 when the wire broke on µs k; `broke` says which).
+template <int H, bool HOT, bool ALIGNED, int W, bool LOG, class LogTick>
+__device__ __forceinline__ int run_quiet(float2 (&T)[H], const Coefs<H, ALIGNED> &co, const float cRf, const float ncL,
+                                         const float spoolf, const LaneFlags &f, EnvCtx<W> &ctx, const int n,
+                                         const float crit_T, const float break_T, int &crit_count, bool &broke,
+                                         bool &cold_after, LogTick &&log_tick)
+{
+    const float2 ncL2 = make_float2(ncL, ncL), cR2 = make_float2(cRf, cRf);
+    const float gate_T = fminf(crit_T, break_T);
     broke = false;
+#ifdef SPARC_ABL_NOSTENCIL
+    if (!HOT) { crit_count = 0; return n; }
+#endif
+    if constexpr (!HOT && !LOG && W == 1) {     // the common case: two µs per trip (halves the loop overhead)
+        int k = 0;
+#pragma unroll 1
+        for (; k + 2 <= n; k += 2) {
+            stencil_quiet_us<H, ALIGNED, W>(T, co, cR2, ncL2, spoolf, f, ctx);
+            stencil_quiet_us<H, ALIGNED, W>(T, co, cR2, ncL2, spoolf, f, ctx);
+        }
+        if (k < n) stencil_quiet_us<H, ALIGNED, W>(T, co, cR2, ncL2, spoolf, f, ctx);
+        crit_count = 0;
+        return n;
+    }
 #pragma unroll 1
     for (int k = 0; k < n; k++) {
-        float left, right;
-        stencil_halos<W>(ctx, T[0].x, T[H - 1].y, left, right, spoolf);
-        // the three differences that cross a half boundary are scalar; the middle one is shared.
-        // Pairs 1..H-2 do not see the halos: they go first so the shuffles complete underneath them;
-        // pair H-1 (needs `right`) and pair 0 (needs `left`) come last.  (Measured: +2 % over the
-        // natural order; issuing the next µs's shuffles in the middle of the body was slower.)
-        const float d_mid = T[0].y - T[H - 1].x;
-        const float2 d0 = sub2(T[1], T[0]);     // dnext of pair 0, dprev of pair 1 (old values)
-        float lmax = spoolf;
-        float2 dprev = d0;
-#pragma unroll
-        for (int j = 1; j < H - 1; j++) {
-            const float2 dnext = sub2(T[j + 1], T[j]);
-            float2 q = __ffma2_rn(cE[j], T[j], c0[j]);
-            q = __ffma2_rn(cR[j], dnext, q);
-            q = __ffma2_rn(ncL2, dprev, q);
-            dprev = dnext;
-            T[j] = __fadd2_rn(T[j], q);
-            if (HOT) lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
-        }
-        {
-            const float2 dlast = make_float2(d_mid, right - T[H - 1].y);
-            float2 q = __ffma2_rn(cE[H - 1], T[H - 1], c0[H - 1]);
-            q = __ffma2_rn(cR[H - 1], dlast, q);
-            q = __ffma2_rn(ncL2, dprev, q);
-            T[H - 1] = __fadd2_rn(T[H - 1], q);
-            if (HOT) lmax = fmaxf(lmax, fmaxf(T[H - 1].x, T[H - 1].y));
-        }
-        {
-            const float2 dfirst = make_float2(T[0].x - left, d_mid);
-            float2 q = __ffma2_rn(cE[0], T[0], c0[0]);
-            q = __ffma2_rn(cR[0], d0, q);
-            q = __ffma2_rn(ncL2, dfirst, q);
-            T[0] = __fadd2_rn(T[0], q);
-            if (HOT) lmax = fmaxf(lmax, fmaxf(T[0].x, T[0].y));
-        }
+        stencil_quiet_us<H, ALIGNED, W>(T, co, cR2, ncL2, spoolf, f, ctx);
         if (LOG) log_tick();
         if (HOT) {
-            const bool hot = vote_any<W>(lmax > crit_T);
+            const float lmax = lane_max<H>(T, f, spoolf);
+            bool hot = false, brk = false;
+            if (vote_any<W>(lmax > gate_T)) {
+                hot = vote_any<W>(lmax > crit_T);
+                brk = vote_any<W>(lmax > break_T);
+            }
             crit_count = hot ? crit_count + 1 : 0;
-            if (hot && vote_any<W>(lmax > break_T)) { broke = true; return k + 1; }
-            if (k == n - 1) cold_after = !vote_any<W>(lmax > crit_T - 1.0f);
+            if (brk) { broke = true; return k + 1; }
+            if (k == n - 1) cold_after = !vote_any<W>(lmax > gate_T - 1.0f);
         }
     }
     if (!HOT) crit_count = 0;
     return n;
 }
 
-// resident blocks per SM the register budget is sized for
+// resident blocks per SM the register budget is sized for (64-thread blocks: 8 -> 16 warps/SM).  Measured in
+// round 2 (profiles/r02_occupancy.txt): the kernel is bound by instruction dispatch, not by latency — 16, 24, 28
+// and 32 warps/SM run at the same cycles per env-us — so registers are not traded for occupancy.
 #ifndef SPARC_MINB_SMALL
-#define SPARC_MINB_SMALL 7
+#define SPARC_MINB_SMALL 8
 #endif
-constexpr int min_blocks_for(int K)
+constexpr int min_blocks_for(int K, bool aligned)
 {
-    return (K <= 13 ? SPARC_MINB_SMALL : (K <= 20 ? 6 : 4)) * 64 / SPARC_BLOCK_THREADS;
+    return ((K <= 20 || aligned) ? SPARC_MINB_SMALL : 6) * 64 / SPARC_BLOCK_THREADS;
 }
 
 #define SPARC_LN2_UP 0.6931471805599460    /* ln2*(1+2^-50): u3 < fl(ln2/den) implies u3*den <= this */
 
 // Wait until the mechanics pre-pass of THIS launch (tag `seq`) has published at least `need` blocks of
-// the env whose progress word is *pp; returns the number published.  Out of line: it runs a handful
-// of times per launch and must not cost the step kernel registers.
+// the env whose progress word is *pp; returns the number published, or 0 after a bounded spin (the
+// caller then computes the trajectory itself, mech_self_serve).  Out of line: it runs a handful of times
+// per launch and must not cost the step kernel registers.
 static __device__ __noinline__ uint32_t mech_wait(const uint32_t *pp, const uint32_t seq, const uint32_t need)
 {
     unsigned spins = 0;
@@ -159,34 +257,60 @@ static __device__ __noinline__ uint32_t mech_wait(const uint32_t *pp, const uint
         const uint32_t d = pv - seq;
         if (d < 64u && d >= need) return d;
         __nanosleep(100);
-        if (++spins > (1u << 23)) __trap();     // ~1 s: the producer is gone — fail loudly, never hang
+        if (++spins > (1u << 21)) return 0;     // ~0.3 s: do not hang and do not kill the context
     }
 }
 
-template <int K, bool INJECT, int W, bool LOG>
-__global__ void __launch_bounds__(W == 1 ? SPARC_BLOCK_THREADS : 32 * W, W == 1 ? min_blocks_for(K) : 1)
-step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
-             const __grid_constant__ StepArgs a)
+// The hand-off timed out (a producer that never ran: debugger, time-slicing, a failed launch): this
+// warp evaluates the recurrence of its own env up to block `need`, from the launch's initial state,
+// with the same operation sequence as mech_kernel's exact path, and writes the same scratch.  Both
+// writers produce identical values, so a slow-but-alive producer does no harm.
+static __device__ __noinline__ void mech_self_serve(const SparcParams &P, const SparcStatePtrs &S, const StepArgs &a,
+                                                    EnvState &s, const uint32_t need)
+{
+    const int e = s.e;
+    double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
+    double *ck = S.mech_ckpt + (size_t)e * SPARC_MECH_NCKPT * 2;
+    double wire = s.wire0, v = S.v[e], pa = S.prev_accel[e];
+    ck[0] = v; ck[1] = pa;
+    const int upto = ((int)need * SPARC_MECH_CKPT < a.n_us) ? (int)need * SPARC_MECH_CKPT : a.n_us;
+    for (int k = 0; k < upto; k++) {
+        mech_step(P, wire, v, pa, (k >= s.first_latch_it) ? s.delta_new0 : s.delta_old0);
+        traj[k] = wire;
+        if ((k + 1) % SPARC_MECH_CKPT == 0) { ck[2 * ((k + 1) / SPARC_MECH_CKPT)] = v; ck[2 * ((k + 1) / SPARC_MECH_CKPT) + 1] = pa; }
+        if (k + 1 == a.n_us) { ck[2 * (SPARC_MECH_NCKPT - 1)] = v; ck[2 * (SPARC_MECH_NCKPT - 1) + 1] = pa; }
+    }
+    __threadfence();
+    __syncwarp();
+    s.mech_self = need;
+    if (a.mech_seq) s.flags |= SPARC_F_HANDOFF_SLOW;
+}
+
+// One environment, start to end of the launch, on the calling warp (W == 1) or block (W > 1).
+template <int K, bool INJECT, int W, bool LOG, bool ALIGNED, int WARPS>
+__device__ __forceinline__ void step_env(const SparcParams &P, const SparcStatePtrs &S, const StepArgs &a, const int e,
+                                         float (&sm_halo)[2][W][2], double (&sm_red)[W], WarpRec (&sm_rec)[WARPS],
+                                         float (&sm_log)[LOG ? WARPS : 1][LOG ? 32 * K + 8 : 1])
 {
     constexpr unsigned FULL = 0xffffffffu;
-    // W == 1: one warp per env, SPARC_BLOCK_THREADS/32 envs per block; W > 1: one block of W warps per env
-    constexpr int WARPS = (W == 1) ? SPARC_BLOCK_THREADS / 32 : W;
-    __shared__ float sm_halo[2][W][2];
-    __shared__ double sm_red[W];
-    __shared__ uint32_t sm_mech_ready[WARPS];
-    __shared__ float sm_log[LOG ? WARPS : 1][LOG ? 32 * (K + 1) : 1];   // field-log staging: coalesced row stores
+    static_assert(K % 2 == 0 && K >= 4, "packed stencil: even number of cells per lane, at least two per half");
+    constexpr int H = K / 2;
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
-    const int e = (W == 1) ? blockIdx.x * WARPS + wib : blockIdx.x;
-    if (e >= a.n_envs) return;                  // whole env group (warp or block)
+#ifdef SPARC_DBG_TIMES
+    unsigned long long dbg_t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+#endif
     EnvCtx<W> ctx;
     ctx.lane = lane; ctx.wid = (W == 1) ? 0 : wib; ctx.gl = ctx.wid * 32 + lane;
     ctx.halo = sm_halo; ctx.parity = 0;
-    const int gl = ctx.gl;                      // lane within the env: owns slots gl*K .. gl*K+K-1
+    const int gl = ctx.gl;                      // lane within the env
+    WarpRec &R = sm_rec[wib];
+    EnvState &s = R.s;
     const uint32_t k0 = (uint32_t)a.seed, k1 = (uint32_t)(a.seed >> 32);
 
-    // ---------------- load ---------------------------------------------------------------------
-    EnvState s;
+    // ---------------- load: scalar state -> the warp's shared-memory record ---------------------
+    // every lane executes the same scalar code and writes the same values (no divergence, no sync)
     s.e = e; s.it = 0; s.writer = gl == 0;
     s.env_id = a.env_id_base + (uint32_t)e;
     s.episode = (uint32_t)S.episode[e];
@@ -199,34 +323,46 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     // launches of one call (it_base > 0: a later mechanics epoch / sampling chunk of the same call)
     const bool cont = a.it_base > 0;
     s.win_sparks = cont ? S.win_sparks[e] : 0;
-    const int win_short0 = cont ? S.win_short_us[e] : 0, win_steps0 = cont ? S.win_steps[e] : 0;
-    s.win_short_us = win_short0;
+    s.win_short0 = cont ? S.win_short_us[e] : 0;
+    s.win_steps0 = cont ? S.win_steps[e] : 0;
+    s.win_short_us = s.win_short0;
     s.dens_valid = true; s.pend_flush = false; s.fast_ok = false;
     s.tsi_prev = 0; s.plasma_idx = -1;
     s.heat_on = false; s.thermal = false; s.refresh = false; s.freeze = false; s.became_done = false;
     s.jA = 0.f; s.jB = 0.f; s.fP = 0.f; s.hb = 0.f; s.he = 0.f;
     s.gap_lo_f = 0.0; s.gap_hi_f = -1.0; s.lo_c = 0.0; s.hi_c = 0.0; s.flush_amt = 0.0; s.onoff_thr = 0;
     derive_generator(s, P, S.target_voltage[e], S.on_time[e], S.off_time[e]);
-
-    double wp = S.wp[e], wire = S.wire[e], v = S.v[e], prev_accel = S.prev_accel[e];
-    double target_delta = S.target_delta[e], voltage = S.voltage[e], debris_volume = S.debris_volume[e];
-    double win_vsum = cont ? S.win_vsum[e] : 0.0, gap_prev = wp - wire;
-    int time = S.time[e], spark_state = S.spark_state[e], spark_dur = S.spark_dur[e], flags = S.flags[e];
-    int crit_count = S.crit_count[e];
-    int w_zone_counter = S.w_zone_counter[e];
-    const int time0 = time;
-    s.latch_time = time - S.t_servo[e];
-    s.tse_ref = time - S.t_spark_end[e];
-    s.ion_end = time + S.ion_rem[e];
-    if (spark_state == 1 && (flags & SPARC_F_HAS_Y))
+    s.wp = S.wp[e]; s.wire = S.wire[e]; s.v = S.v[e]; s.prev_accel = S.prev_accel[e];
+    s.fin_wire = s.wire; s.fin_v = s.v; s.fin_pa = s.prev_accel;
+    s.target_delta = S.target_delta[e]; s.voltage = S.voltage[e]; s.debris_volume = S.debris_volume[e];
+    s.win_vsum = cont ? S.win_vsum[e] : 0.0;
+    s.gap_prev = s.wp - s.wire;
+    s.time = S.time[e]; s.spark_state = S.spark_state[e]; s.spark_dur = S.spark_dur[e]; s.flags = S.flags[e];
+    s.crit_count = S.crit_count[e];
+    s.w_zone_counter = S.w_zone_counter[e];
+    s.time0 = s.time;
+    s.latch_time = s.time - S.t_servo[e];
+    s.tse_ref = s.time - S.t_spark_end[e];
+    s.ion_end = s.time + S.ion_rem[e];
+    if (s.spark_state == 1 && (s.flags & SPARC_F_HAS_Y))
         s.plasma_idx = (P.segment_len != 0.0) ? P.zone_start + (int)py_floordiv(S.spark_y[e], P.segment_len) : P.zone_start;
 
-    if (flags & SPARC_F_DONE) {                 // terminated envs are left untouched
+    const int N = P.n_segments;
+    float spoolf = (float)P.spool_T;
+    asm volatile("" : "+f"(spoolf));            // keep it in a register (no per-µs F2F rematerialisation)
+    const LaneGeom geom = lane_geom(a.lay, gl, H);
+    LaneFlags lf;
+    lf.first = gl == 0;
+    lf.short_x = geom.nx == H - 1; lf.short_y = geom.ny == H - 1;
+    lf.empty_x = geom.nx == 0; lf.empty_y = geom.ny == 0;
+    lf.end_x = (2 * gl == a.lay.hb[3] - 1); lf.end_y = (2 * gl + 1 == a.lay.hb[3] - 1);
+    float *Trow = S.T + (size_t)e * S.n_pad;
+
+    if (s.flags & SPARC_F_DONE) {               // terminated envs are left untouched
         if (s.writer && !cont) { S.win_vsum[e] = 0.0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0; }
         if (a.obs) {                            // observation of a frozen env, from the stored state
             float m = -3.0e38f;
-            const float *row = S.T + (size_t)e * S.n_pad;
-            for (int c = gl; c < P.n_segments; c += 32 * W) m = fmaxf(m, row[c]);
+            for (int c = gl; c < N; c += 32 * W) m = fmaxf(m, Trow[c]);
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
             if constexpr (W > 1) {
@@ -236,49 +372,50 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             }
             if (s.writer) {
                 const size_t ne = (size_t)a.n_envs;
-                const int steps = cont ? win_steps0 : 0;
-                a.obs[0 * ne + e] = (float)(wp - wire);
-                a.obs[1 * ne + e] = (float)v;
-                a.obs[2 * ne + e] = steps > 0 ? (float)(win_vsum / (double)steps) : 0.0f;
+                const int steps = cont ? s.win_steps0 : 0;
+                a.obs[0 * ne + e] = (float)(s.wp - s.wire);
+                a.obs[1 * ne + e] = (float)s.v;
+                a.obs[2 * ne + e] = steps > 0 ? (float)(s.win_vsum / (double)steps) : 0.0f;
                 a.obs[3 * ne + e] = (float)s.win_sparks;
                 a.obs[4 * ne + e] = (float)s.win_short_us;
                 a.obs[5 * ne + e] = m;
                 a.obs[6 * ne + e] = (float)s.debris_density;
-                a.obs[7 * ne + e] = (float)flags;
+                a.obs[7 * ne + e] = (float)s.flags;
+                a.obs[8 * ne + e] = __int_as_float(s.time);
+                a.obs[9 * ne + e] = __int_as_float(s.spark_state);
+                a.obs[10 * ne + e] = __int_as_float(s.time - s.latch_time);
+                a.obs[11 * ne + e] = 0.0f;
             }
         }
         return;
     }
 
-    int next_latch = s.latch_time + P.servo_interval;
-    bool fast_ok = false, ran_fast = false, zone_mean_written = false, done = false;
-    int skip_flush = 0;                         // 1: the next quiet run starts with no pending debris flush
-    int tsi_break = -1;
+    s.next_latch = s.latch_time + P.servo_interval;
+    s.ran_fast = false; s.zone_mean_written = false; s.done = false;
+    s.skip_flush = 0;                           // 1: the next quiet run starts with no pending debris flush
+    s.tsi_break = -1;
+    s.rng_valid = false; s.rng_cbase = 0;
+    s.mech_ready = 0; s.mech_self = 0;
 
     // upper bound of lambda(gap) = ln2/(a g^2 + b g + c) over all gaps (ignition.py:348-364): a
     // draw above it can never ignite, whatever the gap.
-    double lam_bound = 2.0;
-    if (P.ignition_a_coeff > 0.0) {
-        double den_min = P.ignition_c_coeff - P.ignition_b_coeff * P.ignition_b_coeff / (4.0 * P.ignition_a_coeff);
-        if (den_min > 0.0) lam_bound = 0.6931471805599453 / den_min * (1.0 + 1e-9);
+    {
+        double lam_bound = 2.0;
+        if (P.ignition_a_coeff > 0.0) {
+            double den_min = P.ignition_c_coeff - P.ignition_b_coeff * P.ignition_b_coeff / (4.0 * P.ignition_a_coeff);
+            if (den_min > 0.0) lam_bound = 0.6931471805599453 / den_min * (1.0 + 1e-9);
+        }
+        uint32_t w_thresh = 0xffffffffu;        // word >= w_thresh  =>  u01(word) >= lam_bound
+        if (lam_bound < 0.999) w_thresh = (uint32_t)(lam_bound * 4294967296.0) + 2u;
+        s.lam_bound = lam_bound; s.w_thresh = w_thresh;
     }
-    uint32_t w_thresh = 0xffffffffu;            // word >= w_thresh  =>  u01(word) >= lam_bound
-    if (lam_bound < 0.999) w_thresh = (uint32_t)(lam_bound * 4294967296.0) + 2u;
 
-    // ---------------- temperature field -> registers -----------------------------------------
-    const int N = P.n_segments;
-    const int M = N - 1;                        // dynamic cells 1..N-1; cell 0 == spool_T
-    float spoolf = (float)P.spool_T;
-    asm volatile("" : "+f"(spoolf));            // keep it in a register (no per-µs F2F rematerialisation)
-    static_assert(K % 2 == 0, "packed stencil needs an even number of cells per lane");
-    constexpr int H = K / 2;
-    float2 T[H];                                // T[j] = (cell j, cell j+H) of this lane's K slots
-    float *Trow = S.T + (size_t)e * S.n_pad;
+    // ---------------- temperature field -> registers (region layout) --------------------------
+    float2 T[H];                                // T[j] = (slot j of the x half, slot j of the y half)
 #pragma unroll
     for (int j = 0; j < H; j++) {
-        const int sa = gl * K + j, sb = sa + H;
-        T[j].x = (sa < M) ? Trow[sa + 1] : spoolf;
-        T[j].y = (sb < M) ? Trow[sb + 1] : spoolf;
+        T[j].x = (j < geom.nx) ? Trow[geom.cx0 + j] : spoolf;
+        T[j].y = (j < geom.ny) ? Trow[geom.cy0 + j] : spoolf;
     }
 
     // ---------------- stencil coefficients ---------------------------------------------------
@@ -289,42 +426,39 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         double adv = 0.0;                       // wire.py:299-309
         if (fabs(unwind_v) > 1e-6) adv = P.density_times_cp * fabs(unwind_v) * P.S;
         if (!(fabs(adv) > 1e-9)) adv = 0.0;     // wire.py:114
-        cRf = (float)(f * P.k_cond_coeff);
+        cRf = P.cond_coeff_f32;                  // (float)(f * k_cond_coeff), rounded on the host
         ncL = -(float)(f * (P.k_cond_coeff + adv));
     }
-    float2 cE[H], c0[H], cR[H];
-    bool convex = false;                        // T' is a convex combination of T, T_diel (no source)
-    auto slot_coeffs = [&](int sl, float hb, float he, float &e_, float &z_, float &r_) {
-        const int i = sl + 1;
-        if (sl < M) {
-            float h = (i >= P.actual_zone_start && i < P.actual_zone_end) ? he : hb;
-            double hA = (double)h * P.A;        // conv_coeff, wire.py:110
-            e_ = (float)(-(f * hA));
-            z_ = (float)(f * hA * P.dielectric_temperature);
-            r_ = (i < N - 1) ? cRf : 0.0f;      // Neumann end, wire.py:95
-        } else {                                // pad slot: pinned near spool_T, feeds nothing
-            e_ = -1.0f;
-            z_ = spoolf;
-            r_ = 0.0f;
-        }
+    const float gate_T = fminf(P.critical_temperature_f32, P.breaking_temperature_f32);
+    Coefs<H, ALIGNED> co;
+    auto conv_pair = [&](float h, float &e_, float &z_) {
+        const double hA = (double)h * P.A;      // conv_coeff, wire.py:110
+        e_ = (float)(-(f * hA));
+        z_ = (float)(f * hA * P.dielectric_temperature);
     };
     auto refresh_coeffs = [&](float hb, float he) {
+        if constexpr (ALIGNED) {
+            co.cE[0] = make_float2(0.f, 0.f); co.c0[0] = make_float2(0.f, 0.f);
+            if (geom.rx >= 0) conv_pair(geom.rx == 1 ? he : hb, co.cE[0].x, co.c0[0].x);
+            if (geom.ry >= 0) conv_pair(geom.ry == 1 ? he : hb, co.cE[0].y, co.c0[0].y);
+        } else {
 #pragma unroll
-        for (int j = 0; j < H; j++) {
-            slot_coeffs(gl * K + j, hb, he, cE[j].x, c0[j].x, cR[j].x);
-            slot_coeffs(gl * K + j + H, hb, he, cE[j].y, c0[j].y, cR[j].y);
+            for (int j = 0; j < H; j++) {
+                co.cE[j] = make_float2(0.f, 0.f); co.c0[j] = make_float2(0.f, 0.f);
+                const int ix = geom.cx0 + j, iy = geom.cy0 + j;
+                if (j < geom.nx) conv_pair((ix >= P.actual_zone_start && ix < P.actual_zone_end) ? he : hb, co.cE[j].x, co.c0[j].x);
+                if (j < geom.ny) conv_pair((iy >= P.actual_zone_start && iy < P.actual_zone_end) ? he : hb, co.cE[j].y, co.c0[j].y);
+            }
         }
         const float hmax = fmaxf(hb, he), hmin = fminf(hb, he);
         const float ce_max = (float)(f * ((double)hmax * P.A));
-        convex = hmin >= 0.0f && cRf >= 0.0f && ncL <= 0.0f && (cRf - ncL + ce_max) <= 0.999f &&
-                 fmaxf((float)P.dielectric_temperature, spoolf) < P.critical_temperature_f32 - 1.0f;
+        // T' is a convex combination of T and T_diel when no source is on: the maximum cannot grow
+        s.convex = hmin >= 0.0f && cRf >= 0.0f && ncL <= 0.0f && (cRf - ncL + ce_max) <= 0.999f &&
+                   fmaxf((float)P.dielectric_temperature, spoolf) < gate_T - 1.0f;
     };
     refresh_coeffs(S.h_base[e], S.h_enh[e]);
-    bool cold_ok = false;                       // max T < critical - 1 K after the last executed µs
+    s.cold_ok = false;                          // max T < gate - 1 K after the last executed µs
 
-    // contact span in slot coordinates of this lane
-    const int j_span_lo = P.contact_bottom_idx - 1 - gl * K;
-    const int j_span_hi = P.contact_top_idx - 1 - gl * K;
     const double *drow = INJECT ? a.draws + ((size_t)e * a.total_us + a.it_base) * SPARC_N_DRAW_SLOTS : nullptr;
 
     // temperature-field logging (SimulationLogger "wire_temperature", utils/logger.py:128-150): row r
@@ -335,19 +469,19 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     int log_row = logging ? a.it_base / a.log_every : 0;                // next row to write
     auto write_log_row = [&](int r) {
         float *row = a.tlog + ((size_t)e * log_rows + r) * N;
-        float *stage = sm_log[wib];             // lane-major with an odd pitch: conflict-free both ways
+        float *stage = sm_log[wib];             // this warp's cells in cell order, first cell at stage[0]
+        const int wfirst = __shfl_sync(FULL, geom.cx0, 0);      // first cell of this warp (lane 0's x half is never empty)
 #pragma unroll
         for (int j = 0; j < H; j++) {
-            stage[lane * (K + 1) + j] = T[j].x;
-            stage[lane * (K + 1) + j + H] = T[j].y;
+            if (j < geom.nx) stage[geom.cx0 - wfirst + j] = T[j].x;
+            if (j < geom.ny) stage[geom.cy0 - wfirst + j] = T[j].y;
         }
         __syncwarp();
-        const int wbase = ctx.wid * 32 * K;     // first slot of this warp; slot s is cell s + 1
+        const int last_c = geom.ny ? geom.cy0 + geom.ny : geom.cx0 + geom.nx;   // one past this lane's last cell (0 if none)
+        int wend = last_c;
 #pragma unroll
-        for (int q = 0; q < K; q++) {
-            const int sl = q * 32 + lane;
-            if (wbase + sl < M) row[wbase + sl + 1] = stage[(sl / K) * (K + 1) + sl % K];
-        }
+        for (int o = 16; o > 0; o >>= 1) wend = max(wend, __shfl_xor_sync(FULL, wend, o));
+        for (int c = wfirst + lane; c < wend; c += 32) row[c] = stage[c - wfirst];
         __syncwarp();
         if (gl == 0) row[0] = spoolf;
     };
@@ -364,65 +498,108 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     // read only after the producer thread of this env has published them through mech_prog
     // (st.release / ld.acquire at GPU scope), and with ld.global.cg — an L1 line fetched before the
     // producer finished it would be stale.  The producer is ~8x faster than this consumer, so after the
-    // first blocks one poll covers many blocks (mech_ready caches the last value seen; the poll
-    // itself is out of line, mech_wait).
+    // first blocks one poll covers many blocks (s.mech_ready caches the last value seen; the poll
+    // itself is out of line, mech_wait).  A poll that times out makes this warp compute its own
+    // trajectory (mech_self_serve) instead of trapping.
     const double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
-    // pre-pass blocks known to be published, per warp, in shared memory (read once per 32-µs block;
-    // a register held across the stencil loops costs more than the LDS)
-    volatile uint32_t *mech_ready = &sm_mech_ready[wib];
-    *mech_ready = 0;
     auto need_mech = [&](int upto_us) {         // positions of launch-µs < upto_us and checkpoints up to there
         const uint32_t need = (uint32_t)((upto_us + SPARC_MECH_CKPT - 1) / SPARC_MECH_CKPT);
-        if (need > *mech_ready) *mech_ready = mech_wait((const uint32_t *)S.mech_prog + e, a.mech_seq, need);
+        if (need > s.mech_ready && need > s.mech_self) {
+            // mech_seq == 0: a launch too short to be worth a second kernel (the drop-in's 1-µs step()):
+            // there is no pre-pass, the warp evaluates the few mechanics steps itself
+            const uint32_t got = a.mech_seq ? mech_wait((const uint32_t *)S.mech_prog + e, a.mech_seq, need) : 0u;
+            if (got) s.mech_ready = got;
+            else mech_self_serve(P, S, a, s, (uint32_t)((a.n_us + SPARC_MECH_CKPT - 1) / SPARC_MECH_CKPT));
+        }
     };
-    const double wire0 = wire, delta_old0 = target_delta, delta_new0 = (double)a.act.servo[e];
-    const int first_latch_it = (next_latch - time > 0) ? next_latch - time : 0;
+    s.wire0 = s.wire; s.delta_old0 = s.target_delta; s.delta_new0 = (double)a.act.servo[e];
+    s.first_latch_it = (s.next_latch - s.time > 0) ? s.next_latch - s.time : 0;
 
-    int it = 0;
-    while (it < a.n_us && !done) {
+    // finished inside a block: exact mechanics state after launch-µs `target`, replayed from the
+    // pre-pass checkpoint (same operation sequence as mech_kernel)
+    auto rewind_mech = [&](int target) {
+        const int c = target / SPARC_MECH_CKPT;
+        const double *ck = S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + c) * 2;
+        double wire = (c == 0) ? s.wire0 : __ldcg(traj + c * SPARC_MECH_CKPT - 1);
+        double v = __ldcg(ck), pa = __ldcg(ck + 1);
+#pragma unroll 1
+        for (int k = c * SPARC_MECH_CKPT; k < target; k++)
+            mech_step(P, wire, v, pa, (k >= s.first_latch_it) ? s.delta_new0 : s.delta_old0);
+        s.fin_wire = wire; s.fin_v = v; s.fin_pa = pa;
+    };
+
+    int it = 0, prev_nb = 0;
+    double nxt_post = 0.0;
+#ifdef SPARC_ABL_ALLQUIET
+    {   // ablation: the whole launch as ONE cold quiet run (stencil speed inside this kernel)
+        bool broke = false, cold_after = true; int cc = 0;
+        run_quiet<H, false, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, a.n_us, 0.f, 0.f, cc, broke, cold_after, log_tick);
+        s.time += a.n_us; it = a.n_us; need_mech(a.n_us);
+    }
+#endif
+    while (it < a.n_us && !s.done) {
         // ================= block setup ==========================================================
         int nb = a.n_us - it;
         if (nb > 32) nb = 32;
-        int to_latch = next_latch - time;
         bool force_general = false;
-        if (to_latch <= 0) {                    // the first µs of this block latches the action
-            to_latch = (P.servo_interval > 1) ? P.servo_interval : 1;
-            force_general = true;
+        {
+            int to_latch = s.next_latch - s.time;
+            if (to_latch <= 0) {                // the first µs of this block latches the action
+                to_latch = (P.servo_interval > 1) ? P.servo_interval : 1;
+                force_general = true;
+            }
+            if (nb > to_latch) nb = to_latch;   // a block never straddles a latch
         }
-        if (nb > to_latch) nb = to_latch;       // a block never straddles a latch
-        // wire positions of this block from the mechanics pre-pass: lane l holds µs it + l
-        need_mech(it + nb);
-        const double post_l = __ldcg(traj + it + ((lane < nb) ? lane : nb - 1));  // wire after µs `lane`
-        double pre_l = __shfl_up_sync(FULL, post_l, 1);                  // wire before µs `lane`
-        if (lane == 0) pre_l = (it == 0) ? wire0 : __ldcg(traj + it - 1);
-        // ignition roll of µs `lane` (slot 2): word (time+lane)&3 of Philox block (time+lane)>>2
-        uint32_t w_l = 0;
+        // wire positions of this block from the mechanics pre-pass: pos[0] before its first µs,
+        // pos[1 + l] after µs l.  They were requested one block AGO (nxt_post: the L2 round trip of
+        // ld.global.cg passes under the previous block's stencil runs; it was the largest single stall
+        // of the scalar phase, profiles/r02_v4_ncu_summary.txt); only the first block of a launch waits.
+        {
+            int upto = it + nb + 32;
+            if (upto > a.n_us) upto = a.n_us;
+            need_mech(upto);                    // this block and the next
+        }
+        {
+            double cur_post, p0;
+            if (it == 0) {
+                cur_post = __ldcg(traj + ((lane < a.n_us) ? lane : a.n_us - 1));
+                p0 = s.wire0;
+            } else {
+                cur_post = nxt_post;            // requested with index it + lane during the previous block
+                p0 = R.pos[prev_nb];            // wire after the last µs of the previous block
+            }
+            int idx = it + nb + lane;
+            if (idx > a.n_us - 1) idx = a.n_us - 1;
+            nxt_post = __ldcg(traj + idx);
+            __syncwarp();
+            R.pos[lane + 1] = cur_post;
+            if (lane == 0) R.pos[0] = p0;
+            prev_nb = nb;
+        }
+        const int blk_time = s.time;
+        // ignition rolls (slot 2): word t&3 of Philox block t>>2; each lane computes one counter of a
+        // 32-counter window and keeps all four words: one refill serves 125..128 µs
         if (!INJECT) {
-            const uint32_t tl = (uint32_t)(time + lane);
-            uint32_t w[4];
-            philox4x32_10(s.env_id, tl >> 2, s.episode, 2u, k0, k1, w);
-            w_l = pick4(w, tl & 3);
+            const uint32_t c_lo = (uint32_t)blk_time >> 2, c_hi = (uint32_t)(blk_time + nb - 1) >> 2;
+            if (!s.rng_valid || c_lo < s.rng_cbase || c_hi - s.rng_cbase >= 32u) {
+                uint32_t w[4];
+                philox4x32_10(s.env_id, c_lo + (uint32_t)lane, s.episode, 2u, k0, k1, w);
+                *reinterpret_cast<uint4 *>(R.rng[lane]) = make_uint4(w[0], w[1], w[2], w[3]);
+                s.rng_cbase = c_lo; s.rng_valid = true;
+            }
         }
-        // finished inside this block: exact mechanics state after `steps` µs of it, replayed from
-        // the pre-pass checkpoint (same operation sequence as mech_kernel)
-        auto rewind_mech = [&](int steps) {
-            const int target = it + steps;
-            const int c = target / SPARC_MECH_CKPT;
-            const double *ck = S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + c) * 2;
-            wire = (c == 0) ? wire0 : __ldcg(traj + c * SPARC_MECH_CKPT - 1);
-            v = __ldcg(ck); prev_accel = __ldcg(ck + 1);
-#pragma unroll 1
-            for (int k = c * SPARC_MECH_CKPT; k < target; k++)
-                mech_step(P, wire, v, prev_accel, (k >= first_latch_it) ? delta_new0 : delta_old0);
-        };
+        __syncwarp();
 
         int i = 0;
         while (i < nb) {
             // ================= look-ahead: length of the quiet run starting at µs i ===========
             int n = 0;
             int off_tr = -1;                    // run offset of the rest -> idle transition µs
-            const double g = wp - pre_l;
-            if (!force_general && fast_ok && (spark_state == 0 || spark_state == -2)) {
+            const int spark_state = s.spark_state;
+            if (!force_general && s.fast_ok && (spark_state == 0 || spark_state == -2)) {
+                const double pre_l = R.pos[lane], post_l = R.pos[lane + 1];
+                const double wp = s.wp, debris_volume = s.debris_volume;
+                const double g = wp - pre_l;
                 const int off = lane - i;
                 // band conditions: the hysteresis bands of the last flow recomputation
                 auto in_band = [&]() {
@@ -435,39 +612,47 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                 // everything else that makes a µs quiet
                 bool ok = lane < nb && !(post_l > wp + 100.0);  // collision µs (wire_edm.py:173-175)
                 if (spark_state == -2) {
-                    off_tr = s.onoff_thr - spark_dur - 1;
+                    off_tr = s.onoff_thr - s.spark_dur - 1;
                     if (off_tr < 0) off_tr = 0;
                 }
-                if (P.compute_zone_mean) ok = ok && (w_zone_counter + off + 1 < P.zone_mean_interval);
+                if (P.compute_zone_mean) ok = ok && (s.w_zone_counter + off + 1 < P.zone_mean_interval);
                 if (INJECT) {
                     if (lane < nb) {
                         const double *d = drow + (size_t)(it + lane) * SPARC_N_DRAW_SLOTS;
                         ok = ok && d[0] >= SPARC_U1_SAFE;
                         if (off > off_tr) {
                             const double u3 = d[2];
-                            if (!(u3 >= lam_bound)) {
+                            if (!(u3 >= s.lam_bound)) {
                                 double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
                                 ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
                             }
                         }
                     }
-                } else if (off > off_tr && w_l < w_thresh) {
-                    // u3 < fl(ln2/den) can only hold if u3*den <= ln2*(1+2^-50)
-                    const double u3 = u01(w_l);
-                    double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
-                    ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
+                } else if (off > off_tr) {
+                    const uint32_t tl = (uint32_t)(blk_time + lane);
+                    const uint32_t w_l = R.rng[((tl >> 2) - s.rng_cbase) & 31u][tl & 3u];
+                    if (w_l < s.w_thresh) {
+                        // u3 < fl(ln2/den) can only hold if u3*den <= ln2*(1+2^-50)
+                        const double u3 = u01(w_l);
+                        double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
+                        ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
+                    }
                 }
                 unsigned stop = __ballot_sync(FULL, !(ok && in_band())) >> i;
                 n = stop ? __ffs(stop) - 1 : 32 - i;
                 if (n == 0 && ((__ballot_sync(FULL, ok) >> i) & 1u)) {
                     // only a band failed on µs i: refresh the hysteresis state in place (light_refresh)
-                    const bool pending = ran_fast || s.pend_flush;
-                    if (light_refresh(s, P, S, __shfl_sync(FULL, g, i), debris_volume, pending)) {
-                        ran_fast = false;
-                        skip_flush = 1;         // the refreshed µs has no pending flush before it
-                        fast_ok = s.fast_ok;
-                        if (fast_ok) {
-                            stop = __ballot_sync(FULL, !(ok && in_band())) >> i;
+                    const bool pending = s.ran_fast || s.pend_flush;
+                    if (light_refresh(s, P, S, wp - R.pos[i], s.debris_volume, pending)) {
+                        s.ran_fast = false;
+                        s.skip_flush = 1;       // the refreshed µs has no pending flush before it
+                        if (s.fast_ok) {
+                            const double dv2 = s.debris_volume;
+                            bool b = g >= s.gap_lo_f && g <= s.gap_hi_f;
+                            double deb_lo = dv2;
+                            if (dv2 > 0.001) deb_lo = dv2 - (double)(off + 1) * s.flush_amt - 1e-14;
+                            b = b && deb_lo >= s.lo_c * g && dv2 <= s.hi_c * g;
+                            stop = __ballot_sync(FULL, !(ok && b)) >> i;
                             n = stop ? __ffs(stop) - 1 : 32 - i;
                         }
                     }
@@ -477,133 +662,144 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
 
             if (n > 0) {
                 // ================= quiet run ===================================================
-                bool broke = false;
-                int nx;
-                const bool cold = cold_ok && convex;
+                bool broke = false, cold_after = s.cold_ok;
+                int nx, crit_count = s.crit_count;
+                const bool cold = s.cold_ok && s.convex;
                 if (!LOG || !logging) {
                     if (cold)
-                        nx = run_quiet<H, false, W, false>(T, cE, c0, cR, ncL, spoolf, ctx, n, 0.f, 0.f, crit_count, broke,
-                                                           cold_ok, log_tick);
+                        nx = run_quiet<H, false, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, n, 0.f, 0.f, crit_count,
+                                                                    broke, cold_after, log_tick);
                     else
-                        nx = run_quiet<H, true, W, false>(T, cE, c0, cR, ncL, spoolf, ctx, n, P.critical_temperature_f32,
-                                                          P.breaking_temperature_f32, crit_count, broke, cold_ok, log_tick);
+                        nx = run_quiet<H, true, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, n, P.critical_temperature_f32,
+                                                                   P.breaking_temperature_f32, crit_count, broke, cold_after, log_tick);
                 } else {
                     if (cold)
-                        nx = run_quiet<H, false, W, LOG>(T, cE, c0, cR, ncL, spoolf, ctx, n, 0.f, 0.f, crit_count, broke,
-                                                         cold_ok, log_tick);
+                        nx = run_quiet<H, false, ALIGNED, W, LOG>(T, co, cRf, ncL, spoolf, lf, ctx, n, 0.f, 0.f, crit_count, broke,
+                                                                  cold_after, log_tick);
                     else
-                        nx = run_quiet<H, true, W, LOG>(T, cE, c0, cR, ncL, spoolf, ctx, n, P.critical_temperature_f32,
-                                                        P.breaking_temperature_f32, crit_count, broke, cold_ok, log_tick);
+                        nx = run_quiet<H, true, ALIGNED, W, LOG>(T, co, cRf, ncL, spoolf, lf, ctx, n, P.critical_temperature_f32,
+                                                                 P.breaking_temperature_f32, crit_count, broke, cold_after, log_tick);
                 }
+                s.crit_count = crit_count;
+                s.cold_ok = cold_after;
                 // scalar bookkeeping of the nx quiet µs (ignition.py:302-319, dielectric.py:104-144)
                 int n_idle = nx;
                 if (spark_state == -2) {
                     if (nx > off_tr) {          // rest -> idle on run offset off_tr
-                        spark_state = 0; spark_dur = 0; flags &= ~SPARC_F_HAS_Y;
+                        s.spark_state = 0; s.spark_dur = 0; s.flags &= ~SPARC_F_HAS_Y;
                         if (s.writer) S.spark_y[e] = -1.0;
                         n_idle = nx - off_tr;
-                    } else { spark_dur += nx; n_idle = 0; }
+                    } else { s.spark_dur += nx; n_idle = 0; }
                 }
-                voltage = (n_idle > 0) ? s.tv_eff : 0.0;
-                win_vsum += (double)n_idle * s.tv_eff;
-                if (debris_volume > 0.001 && s.flush_amt > 0.0) {
+                s.voltage = (n_idle > 0) ? s.tv_eff : 0.0;
+                s.win_vsum += (double)n_idle * s.tv_eff;
+                {
+                    double dv = s.debris_volume;
+                    if (dv > 0.001 && s.flush_amt > 0.0) {
+                        const double fa = s.flush_amt;
 #pragma unroll 1
-                    for (int k = skip_flush; k < nx && debris_volume > 0.001; k++) debris_volume = debris_volume - s.flush_amt;
+                        for (int k = s.skip_flush; k < nx && dv > 0.001; k++) dv = dv - fa;
+                        s.debris_volume = dv;
+                    }
                 }
-                skip_flush = 0;
-                gap_prev = __shfl_sync(FULL, g, i + nx - 1);
-                ran_fast = true;
-                if (P.compute_zone_mean) w_zone_counter += nx;
+                s.skip_flush = 0;
+                s.gap_prev = s.wp - R.pos[i + nx - 1];
+                s.ran_fast = true;
+                if (P.compute_zone_mean) s.w_zone_counter += nx;
                 if (broke) {                    // wire_edm.py:129-130 on the last µs of the run
-                    flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
-                    tsi_break = 0;
-                    done = true;
-                    time += nx - 1;
-                    rewind_mech(i + nx - 1);
+                    s.flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
+                    s.tsi_break = 0;
+                    s.done = true;
+                    s.time += nx - 1;
+                    rewind_mech(it + i + nx - 1);
                     break;
                 }
-                time += nx;
+                s.time += nx;
                 i += nx;
                 continue;
             }
 
             // ================= general µs ======================================================
-            s.wp = wp; s.wire = __shfl_sync(FULL, pre_l, i); s.v = 0.0; s.prev_accel = 0.0;
-            s.target_delta = target_delta;
-            s.voltage = voltage; s.debris_volume = debris_volume; s.win_vsum = win_vsum; s.gap_prev = gap_prev;
-            s.time = time; s.spark_state = spark_state; s.spark_dur = spark_dur; s.flags = flags;
+            s.wire = R.pos[i];
             s.it = it + i;
-            if (ran_fast) { s.dens_valid = false; s.pend_flush = true; ran_fast = false; }
-            skip_flush = 0;
+            if (s.ran_fast) { s.dens_valid = false; s.pend_flush = true; s.ran_fast = false; }
+            s.skip_flush = 0;
             general_pre<INJECT>(s, P, S, a);
-            wp = s.wp; target_delta = s.target_delta; voltage = s.voltage; debris_volume = s.debris_volume;
-            win_vsum = s.win_vsum; gap_prev = s.gap_prev;
-            spark_state = s.spark_state; spark_dur = s.spark_dur; flags = s.flags;
-            next_latch = s.latch_time + P.servo_interval;
-            fast_ok = s.fast_ok;
+            s.next_latch = s.latch_time + P.servo_interval;
             if (s.refresh) refresh_coeffs(s.hb, s.he);
             if (s.freeze) {                     // crater-table miss: frozen before the thermal update
-                done = true;
-                rewind_mech(i);
+                s.done = true;
+                rewind_mech(it + i);
                 break;
             }
             // ---- compute_thermal_update with sources (wire.py:58-123) -------------------------
-            float lmax = spoolf;
             {
-                float left, right;
-                stencil_halos<W>(ctx, T[0].x, T[H - 1].y, left, right, spoolf);
+                float left, right, xl, yv;
+                stencil_edges<H, W, !ALIGNED>(ctx, T, lf, spoolf, left, right, xl, yv);
                 float2 acc[H];
 #pragma unroll
-                for (int j = 0; j < H; j++) acc[j] = __ffma2_rn(cE[j], T[j], c0[j]);
+                for (int j = 0; j < H; j++) acc[j] = __ffma2_rn(co.e(j), T[j], co.z(j));
                 if (s.heat_on) {
                     const float jA = s.jA, jB = s.jB, fP = s.fP;
-                    const int jp = (s.spark_state == 1 && s.plasma_idx >= 0 && s.plasma_idx < N)
-                                       ? s.plasma_idx - 1 - gl * K : -(1 << 20);
+                    const int pidx = (s.spark_state == 1 && s.plasma_idx >= 0 && s.plasma_idx < N) ? s.plasma_idx : -(1 << 20);
+                    // contact span and plasma cell in slot coordinates of each half
+                    const int xlo = P.contact_bottom_idx - geom.cx0, xhi = P.contact_top_idx - geom.cx0, xp = pidx - geom.cx0;
+                    const int ylo = P.contact_bottom_idx - geom.cy0, yhi = P.contact_top_idx - geom.cy0, yp = pidx - geom.cy0;
 #pragma unroll
                     for (int j = 0; j < H; j++) {
-                        if (j >= j_span_lo && j <= j_span_hi) acc[j].x += fmaf(jA, T[j].x, jB);
-                        if (j == jp) acc[j].x += fP;
-                        if (j + H >= j_span_lo && j + H <= j_span_hi) acc[j].y += fmaf(jA, T[j].y, jB);
-                        if (j + H == jp) acc[j].y += fP;
+                        if (j < geom.nx) {
+                            if (j >= xlo && j <= xhi) acc[j].x += fmaf(jA, T[j].x, jB);
+                            if (j == xp) acc[j].x += fP;
+                        }
+                        if (j < geom.ny) {
+                            if (j >= ylo && j <= yhi) acc[j].y += fmaf(jA, T[j].y, jB);
+                            if (j == yp) acc[j].y += fP;
+                        }
                     }
                 }
-                const float2 ncL2 = make_float2(ncL, ncL);
-                const float d_mid = T[0].y - T[H - 1].x;
+                const float2 ncL2 = make_float2(ncL, ncL), cR2 = make_float2(cRf, cRf);
+                const float d_mid = yv - xl;
                 float2 dprev = make_float2(T[0].x - left, d_mid);
                 const float2 dlast = make_float2(d_mid, right - T[H - 1].y);
 #pragma unroll
                 for (int j = 0; j < H; j++) {
                     const float2 dnext = (j + 1 < H) ? sub2(T[j + 1], T[j]) : dlast;
-                    float2 q = __ffma2_rn(cR[j], dnext, acc[j]);
+                    float2 q = __ffma2_rn(cR2, dnext, acc[j]);
                     q = __ffma2_rn(ncL2, dprev, q);
                     dprev = dnext;
                     T[j] = __fadd2_rn(T[j], q);
-                    lmax = fmaxf(lmax, fmaxf(T[j].x, T[j].y));
                 }
             }
             if (LOG && logging) log_tick();
             // ---- _check_wire_breaking (wire.py:376-388) ---------------------------------------
-            cold_ok = !vote_any<W>(lmax > P.critical_temperature_f32 - 1.0f);
             bool hot = false, brk = false;
-            if (!cold_ok) {
-                hot = vote_any<W>(lmax > P.critical_temperature_f32);
-                if (hot) brk = vote_any<W>(lmax > P.breaking_temperature_f32);
+            {
+                const float lmax = lane_max<H>(T, lf, spoolf);
+                s.cold_ok = !vote_any<W>(lmax > gate_T - 1.0f);
+                if (!s.cold_ok) {
+                    hot = vote_any<W>(lmax > P.critical_temperature_f32);
+                    brk = vote_any<W>(lmax > P.breaking_temperature_f32);
+                }
             }
-            crit_count = hot ? crit_count + 1 : 0;
+            s.crit_count = hot ? s.crit_count + 1 : 0;
             // zone mean (wire.py:338-347, 390-394), only when enabled
             if (P.compute_zone_mean) {
-                w_zone_counter += 1;
-                if (w_zone_counter >= P.zone_mean_interval) {
+                s.w_zone_counter += 1;
+                if (s.w_zone_counter >= P.zone_mean_interval) {
                     int za = P.actual_zone_start, zb = P.actual_zone_end;
                     if (!(zb > za && zb <= N)) { za = 0; zb = N; }
-                    float part = 0.0f;
+                    double tot = 0.0;
 #pragma unroll
-                    for (int jj = 0; jj < K; jj++) {     // ascending cell order within the lane
-                        int c = gl * K + jj + 1;
-                        if (c >= za && c < zb) part += (jj < H) ? T[jj].x : T[jj - H].y;
+                    for (int j = 0; j < H; j++) {
+                        const int cx = geom.cx0 + j;
+                        if (j < geom.nx && cx >= za && cx < zb) tot += (double)T[j].x;
                     }
-                    if (gl == 0 && za == 0) part += spoolf;    // cell 0 when the zone starts at 0
-                    double tot = (double)part;
+#pragma unroll
+                    for (int j = 0; j < H; j++) {
+                        const int cy = geom.cy0 + j;
+                        if (j < geom.ny && cy >= za && cy < zb) tot += (double)T[j].y;
+                    }
+                    if (gl == 0 && za == 0) tot += (double)spoolf;  // cell 0 when the zone starts at 0
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(FULL, tot, o);
                     if constexpr (W > 1) {      // sum of the warps' partial sums, in warp order
@@ -614,79 +810,86 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
                         for (int w = 0; w < W; w++) tot += sm_red[w];
                         __syncthreads();
                     }
-                    double zm = (double)(float)(tot / (double)(zb - za));
+                    const double zm = (double)(float)(tot / (double)(zb - za));
                     if (s.writer) { S.w_last_zone_mean[e] = zm; S.wire_avg_T[e] = zm; }
-                    zone_mean_written = true;
-                    w_zone_counter = 0;
+                    s.zone_mean_written = true;
+                    s.w_zone_counter = 0;
                 }
             }
             if (brk) {
                 // wire_edm.py:129-130: early return, no mechanics, no time bookkeeping
-                flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
-                tsi_break = s.tsi_prev;
-                done = true;
-                rewind_mech(i);
+                s.flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
+                s.tsi_break = s.tsi_prev;
+                s.done = true;
+                rewind_mech(it + i);
                 break;
             }
-            // mechanics of this µs is post_l of lane i; time bookkeeping (wire_edm.py:134-144)
-            time += 1;
-            if (spark_state == 1) s.tse_ref = time;
+            // mechanics of this µs is pos[i + 1]; time bookkeeping (wire_edm.py:134-144)
+            s.time += 1;
+            if (s.spark_state == 1) s.tse_ref = s.time;
             // ---- _check_termination (wire_edm.py:172-179) -------------------------------------
-            const double wire_after = __shfl_sync(FULL, post_l, i);
-            if (wire_after > wp + 100.0) { flags |= SPARC_F_BROKEN; done = true; }
-            else if (wp >= P.target_position) { flags |= SPARC_F_TARGET; done = true; }
-            if (done) { rewind_mech(i + 1); break; }
+            if (R.pos[i + 1] > s.wp + 100.0) { s.flags |= SPARC_F_BROKEN; s.done = true; }
+            else if (s.wp >= P.target_position) { s.flags |= SPARC_F_TARGET; s.done = true; }
+            if (s.done) { rewind_mech(it + i + 1); break; }
             i += 1;
         }
         it += nb;
     }
-    if (!done) {                                // end-of-launch mechanics state from the pre-pass
-        wire = __ldcg(traj + a.n_us - 1);       // published: the last block of the loop waited for it
-        v = __ldcg(S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2);
-        prev_accel = __ldcg(S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2 + 1);
+    if (!s.done) {                              // end-of-launch mechanics state from the pre-pass
+        s.fin_wire = __ldcg(traj + a.n_us - 1); // published: the last block of the loop waited for it
+        s.fin_v = __ldcg(S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2);
+        s.fin_pa = __ldcg(S.mech_ckpt + ((size_t)e * SPARC_MECH_NCKPT + (SPARC_MECH_NCKPT - 1)) * 2 + 1);
     }
-    if (LOG && logging && done) {               // rows sampled at or after termination: the frozen field
+    if (LOG && logging && s.done) {             // rows sampled at or after termination: the frozen field
         for (int r = log_row; r < log_rows; r++) write_log_row(r);
     }
 
+#ifdef SPARC_DBG_TIMES   /* experiments: when and where each env ran, in the unused tail of its trajectory scratch */
+    if (gl == 0 && a.n_us <= 1000) {
+        unsigned long long t1; uint32_t smid, wid;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        asm volatile("mov.u32 %0, %%warpid;" : "=r"(wid));
+        double *dbg = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH + 1016;
+        dbg[0] = (double)dbg_t0; dbg[1] = (double)t1; dbg[2] = (double)smid; dbg[3] = (double)wid;
+    }
+#endif
     // ---------------- store ------------------------------------------------------------------
 #pragma unroll
     for (int j = 0; j < H; j++) {
-        const int sa = gl * K + j, sb = sa + H;
-        if (sa < M) Trow[sa + 1] = T[j].x;
-        if (sb < M) Trow[sb + 1] = T[j].y;
+        if (j < geom.nx) Trow[geom.cx0 + j] = T[j].x;
+        if (j < geom.ny) Trow[geom.cy0 + j] = T[j].y;
     }
     if (gl == 0) {
-        const bool thermal_break = (flags & SPARC_F_THERMAL_BREAK) != 0 && tsi_break >= 0;   // broke in THIS call
-        const int win_steps = (time - time0) + (thermal_break ? 1 : 0);
+        const int flags = s.flags, time = s.time, spark_state = s.spark_state, spark_dur = s.spark_dur;
+        const bool thermal_break = (flags & SPARC_F_THERMAL_BREAK) != 0 && s.tsi_break >= 0;   // broke in THIS call
+        const int win_steps = (time - s.time0) + (thermal_break ? 1 : 0);
         if (win_steps > 0 || (flags & SPARC_F_MODE_ERROR)) {
             // bring the lazily kept dielectric state to what the reference holds after its last µs
-            s.debris_volume = debris_volume; s.gap_prev = gap_prev;
-            if (ran_fast) { s.dens_valid = false; s.pend_flush = true; }
+            if (s.ran_fast) { s.dens_valid = false; s.pend_flush = true; }
             materialize(s, P);
-            debris_volume = s.debris_volume;
         }
         Trow[0] = spoolf;
-        S.wp[e] = wp; S.wire[e] = wire; S.v[e] = v; S.prev_accel[e] = prev_accel;
-        S.voltage[e] = voltage;
+        S.wp[e] = s.wp; S.wire[e] = s.fin_wire; S.v[e] = s.fin_v; S.prev_accel[e] = s.fin_pa;
+        S.voltage[e] = s.voltage;
         S.current[e] = (spark_state == 1 || spark_state == -1) ? s.ipk : 0.0;
-        S.target_delta[e] = target_delta;
-        S.debris_volume[e] = debris_volume; S.debris_density[e] = s.debris_density;
+        S.target_delta[e] = s.target_delta;
+        S.debris_volume[e] = s.debris_volume; S.debris_density[e] = s.debris_density;
         if (win_steps > 0) {
-            double gq = (gap_prev > 0.001) ? gap_prev : 0.001;
+            const double gq = (s.gap_prev > 0.001) ? s.gap_prev : 0.001;
             S.cavity_volume[e] = P.cavity_volume_coeff * (gq * 0.001);     // dielectric.py:91-92
         }
         S.flow[e] = s.flow;
         if (!(spark_state == 1 && spark_dur == 0) && win_steps > 0) S.last_crater_volume[e] = 0.0;
         S.d_last_gap[e] = s.d_last_gap; S.d_last_density[e] = s.d_last_density;
         S.w_last_flow[e] = s.w_last_flow;
-        if (P.compute_zone_mean && win_steps > 0 && !zone_mean_written) S.wire_avg_T[e] = S.w_last_zone_mean[e];
-        S.win_vsum[e] = win_vsum;
+        if (P.compute_zone_mean && win_steps > 0 && !s.zone_mean_written) S.wire_avg_T[e] = S.w_last_zone_mean[e];
+        S.win_vsum[e] = s.win_vsum;
         S.time[e] = time; S.t_servo[e] = time - s.latch_time; S.t_open_v[e] = time;
         // time_since_spark_ignition (wire_edm.py:139-144): dur+1 while sparking, else 0; the
         // µs that returns early (thermal break / mode error) leaves the previous value
         int tsi = (spark_state == 1) ? spark_dur + 1 : 0;
-        if (thermal_break) tsi = tsi_break;
+        if (thermal_break) tsi = s.tsi_break;
         else if (flags & SPARC_F_THERMAL_BREAK) tsi = S.t_spark_ign[e];
         if (flags & SPARC_F_MODE_ERROR) tsi = 0;
         S.t_spark_ign[e] = tsi;
@@ -697,18 +900,17 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
             int ir = s.ion_end - time - (thermal_break ? 1 : 0);
             S.ion_rem[e] = ir > 0 ? ir : 0;
         }
-        S.crit_count[e] = crit_count;
+        S.crit_count[e] = s.crit_count;
         S.current_mode[e] = s.current_mode;
-        S.w_zone_counter[e] = w_zone_counter; S.flags[e] = flags;
-        S.stat_short_us[e] += s.win_short_us - win_short0;
+        S.w_zone_counter[e] = s.w_zone_counter; S.flags[e] = flags;
+        S.stat_short_us[e] += s.win_short_us - s.win_short0;
         S.stat_steps[e] += win_steps;
-        S.win_sparks[e] = s.win_sparks; S.win_short_us[e] = s.win_short_us; S.win_steps[e] = win_steps0 + win_steps;
+        S.win_sparks[e] = s.win_sparks; S.win_short_us[e] = s.win_short_us; S.win_steps[e] = s.win_steps0 + win_steps;
+        s.win_steps_out = win_steps;
     }
     // ---------------- observation summary (what sparc_observe computes from the stored state) ----
     if (a.obs) {
-        float m = spoolf;                       // cell 0; pad slots never exceed the real maximum
-#pragma unroll
-        for (int j = 0; j < H; j++) m = fmaxf(m, fmaxf(T[j].x, T[j].y));
+        float m = lane_max<H>(T, lf, spoolf);   // cell 0 is spoolf
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
         if constexpr (W > 1) {
@@ -719,15 +921,48 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
         }
         if (gl == 0) {
             const size_t ne = (size_t)a.n_envs;
-            const int steps = S.win_steps[e];
-            a.obs[0 * ne + e] = (float)(wp - wire);
-            a.obs[1 * ne + e] = (float)v;
-            a.obs[2 * ne + e] = steps > 0 ? (float)(win_vsum / (double)steps) : 0.0f;
+            const int steps = s.win_steps0 + s.win_steps_out;
+            a.obs[0 * ne + e] = (float)(s.wp - s.fin_wire);
+            a.obs[1 * ne + e] = (float)s.fin_v;
+            a.obs[2 * ne + e] = steps > 0 ? (float)(s.win_vsum / (double)steps) : 0.0f;
             a.obs[3 * ne + e] = (float)s.win_sparks;
             a.obs[4 * ne + e] = (float)s.win_short_us;
             a.obs[5 * ne + e] = m;
             a.obs[6 * ne + e] = (float)s.debris_density;
-            a.obs[7 * ne + e] = (float)flags;
+            a.obs[7 * ne + e] = (float)s.flags;
+            a.obs[8 * ne + e] = __int_as_float(s.time);
+            a.obs[9 * ne + e] = __int_as_float(s.spark_state);
+            a.obs[10 * ne + e] = __int_as_float(s.time - s.latch_time);
+            a.obs[11 * ne + e] = 0.0f;
+        }
+    }
+}
+
+// Each warp (W == 1) or block (W > 1) takes environments e, e + stride, ...; the host launches one per env.
+// (A grid capped at the resident blocks was measured and rejected, profiles/r02_experiments.txt: the
+// hardware's own refill of freed slots balances equal-length envs just as well, and a capped grid delays the
+// blocks that wait for the registers of the pre-pass kernel.)
+template <int K, bool INJECT, int W, bool LOG, bool ALIGNED>
+__global__ void __launch_bounds__(W == 1 ? SPARC_BLOCK_THREADS : 32 * W, W == 1 ? min_blocks_for(K, ALIGNED) : 1)
+step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
+            const __grid_constant__ StepArgs a)
+{
+    // W == 1: one warp per env, SPARC_BLOCK_THREADS/32 envs per block at a time; W > 1: one block of W warps per env
+    constexpr int WARPS = (W == 1) ? SPARC_BLOCK_THREADS / 32 : W;
+    __shared__ float sm_halo[2][W][2];
+    __shared__ double sm_red[W];
+    __shared__ WarpRec sm_rec[WARPS];
+    __shared__ float sm_log[LOG ? WARPS : 1][LOG ? 32 * K + 8 : 1];   // field-log staging, in cell order
+    if constexpr (W == 1) {
+        const int stride = (int)gridDim.x * WARPS;
+        for (int e = (int)blockIdx.x * WARPS + (int)(threadIdx.x >> 5); e < a.n_envs; e += stride) {
+            step_env<K, INJECT, W, LOG, ALIGNED, WARPS>(P, S, a, e, sm_halo, sm_red, sm_rec, sm_log);
+            __syncwarp();
+        }
+    } else {
+        for (int e = (int)blockIdx.x; e < a.n_envs; e += (int)gridDim.x) {
+            step_env<K, INJECT, W, LOG, ALIGNED, WARPS>(P, S, a, e, sm_halo, sm_red, sm_rec, sm_log);
+            __syncthreads();
         }
     }
 }

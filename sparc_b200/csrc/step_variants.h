@@ -12,7 +12,7 @@ using StepFn = void (*)(const SparcParams, const SparcStatePtrs, const StepArgs)
 struct StepVariant {
     int K;              // cells per lane (even: the stencil is two-wide)
     int W;              // warps per environment (1: warp per env, several envs per block; > 1: block per env)
-    StepFn fn[2][2];    // [LOG][INJECT]
+    StepFn fn[2][2][2]; // [LOG][INJECT][ALIGNED]
 };
 
 // mechanics pre-pass of one launch epoch (mech_kernel.cu)
@@ -24,6 +24,9 @@ const StepVariant *step_variants_w4(int *n);
 const StepVariant *step_variants_w8(int *n);
 }  // namespace sparc
 
-#define SPARC_STEP_VARIANT(K, W)                                                                       \
-    {K, W, {{sparc::step_kernel<K, false, W, false>, sparc::step_kernel<K, true, W, false>},           \
-            {sparc::step_kernel<K, false, W, true>, sparc::step_kernel<K, true, W, true>}}}
+#define SPARC_STEP_VARIANT(K, W)                                                                                      \
+    {K, W,                                                                                                            \
+     {{{sparc::step_kernel<K, false, W, false, false>, sparc::step_kernel<K, false, W, false, true>},                  \
+       {sparc::step_kernel<K, true, W, false, false>, sparc::step_kernel<K, true, W, false, true>}},                   \
+      {{sparc::step_kernel<K, false, W, true, false>, sparc::step_kernel<K, false, W, true, true>},                    \
+       {sparc::step_kernel<K, true, W, true, false>, sparc::step_kernel<K, true, W, true, true>}}}}

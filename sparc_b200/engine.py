@@ -207,6 +207,26 @@ class Engine:
     def host_actions(self) -> Dict[str, torch.Tensor]:
         return self._act_host
 
+    def host_stepper(self, n_us: int):
+        """`step_host(n_us)` with every ctypes argument built once: returns a zero-argument callable that
+        runs one `sparc_step_host` (H2D of the pinned action arrays, n_us steps, D2H of the observation,
+        stream sync) and leaves the result in `obs_host`.  For per-µs callers (the drop-in
+        `WireEDMEnv.step`) the per-call Python overhead of `step_host` is larger than the GPU work.
+        The stream and seed are captured now; the caller's current device must be this engine's."""
+        a = self._actions_struct(self._act_host)
+        fn = self.lib.sparc_step_host
+        if torch.cuda.current_device() != (self.device.index or 0):
+            return lambda: self.step_host(n_us)
+        args = (C.c_void_p(self.blob.data_ptr()), C.byref(self.params), C.byref(a), self.n_envs, int(n_us),
+                C.c_uint64(self.seed), C.c_uint32(self.env_id_base), C.c_void_p(self._scratch.data_ptr()),
+                C.c_void_p(self.obs_host.data_ptr()), C.c_void_p(self._stream()))
+
+        def call(_fn=fn, _args=args, _keep=a):
+            rc = _fn(*_args)
+            if rc:
+                N.check(rc)
+        return call
+
     def observe(self) -> torch.Tensor:
         """[8, n_envs] float32 device tensor: gap, wire velocity, mean voltage of the last call,
         sparks and short-circuit µs in the last call, max wire temperature, debris density, flags."""

@@ -50,6 +50,7 @@ class BatchedWireEDMEnv:
         self.auto_reset = bool(auto_reset)
         self.params = derive_params(self.config, mechanics_control_mode, ignition_params, wire_params,
                                     material_params, dielectric_params, mechanics_params)
+        self.base_flow_rate = float((dielectric_params or DielectricModuleParameters()).base_flow_rate)
         self.engine = Engine(self.n_envs, self.params, device=device, seed=seed, env_id_base=env_id_base)
         self._valid_modes = sorted(int(k[1:]) for k in load_craters())
         self._arm_latch(None)

@@ -59,6 +59,7 @@ class WireEDMEnv(EnvBase):
         self._engine = Engine(1, self._params, device=device, seed=int(self.np_random.integers(0, 2**63 - 1)))
         self.state = DeviceStateView(self._engine, 0, self.dielectric.params.base_flow_rate,
                                      self.dielectric.params.dielectric_temperature)
+        self._bind()
 
         self.action_space = Dict({
             "servo": Box(low=-1.0, high=1.0, shape=(1,), dtype=np.float32),
@@ -78,20 +79,41 @@ class WireEDMEnv(EnvBase):
             self.np_random = np.random.default_rng(seed)
             self._engine.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
         self._engine.reset(None, reseed=seed is not None)
+        self._bind()
         return self._get_obs(), {}
+
+    def _bind(self):
+        """(Re)build the per-call fast path: numpy views of the pinned action / observation buffers and
+        the prebuilt C-ABI calls.  The reference's step() costs ~25 µs of host time per simulated µs
+        (wire_edm.py:116-157); a 1-µs launch can only compete if the Python side adds almost nothing:
+        five scalar writes into pinned memory, ONE `sparc_step_host` (one H2D copy, one kernel — a
+        launch this short skips the mechanics pre-pass kernel —, one D2H copy of the observation row,
+        one stream sync), four scalar reads."""
+        e = self._engine
+        ha = e.host_actions
+        self._h_servo, self._h_tv = ha["servo"].numpy(), ha["target_voltage"].numpy()
+        self._h_mode, self._h_on, self._h_off = ha["current_mode"].numpy(), ha["on_time"].numpy(), ha["off_time"].numpy()
+        self._obs_f = e.obs_host.numpy()
+        self._obs_i = self._obs_f.view(np.int32)
+        self._step1 = e.host_stepper(1)
+        self._stepN = e.host_stepper(self.servo_interval)
+        self._flags, self._t_servo = 0, 0           # fresh EDMState: no flags, time_since_servo = 0
+
+    @staticmethod
+    def _first(x):
+        try:
+            return x[0]
+        except (TypeError, IndexError):
+            return x
 
     def _stage(self, action):
         gc = action["generator_control"]
-        self._engine.set_actions(np.asarray(action["servo"]).reshape(-1)[:1], np.asarray(gc["target_voltage"]).reshape(-1)[:1],
-                                 np.asarray(gc["current_mode"]).reshape(-1)[:1], np.asarray(gc["ON_time"]).reshape(-1)[:1],
-                                 np.asarray(gc["OFF_time"]).reshape(-1)[:1])
-
-    def _readback(self):
-        e = self._engine
-        import torch
-
-        v = torch.stack([e["flags"][0], e["time"][0], e["spark_state"][0], e["t_servo"][0]]).cpu().tolist()
-        return int(v[0]), int(v[1]), int(v[2]), int(v[3])
+        f = self._first
+        self._h_servo[0] = f(action["servo"])
+        self._h_tv[0] = f(gc["target_voltage"])
+        self._h_mode[0] = f(gc["current_mode"])
+        self._h_on[0] = f(gc["ON_time"])
+        self._h_off[0] = f(gc["OFF_time"])
 
     def _raise_mode_error(self):
         m = int(self._engine["current_mode"][0].item())
@@ -100,12 +122,12 @@ class WireEDMEnv(EnvBase):
 
     def step(self, action):
         """ONE microsecond (wire_edm.py:116-157)."""
-        flags0, _, _, t_servo0 = self._readback()
-        is_ctrl_step = t_servo0 >= self.servo_interval
-        broken_before = bool(flags0 & N.F_BROKEN)       # wire.update early-outs, step returns at :129-130
+        is_ctrl_step = self._t_servo >= self.servo_interval
+        broken_before = self._flags & N.F_BROKEN        # wire.update early-outs, step returns at :129-130
         self._stage(action)
-        self._engine.step(1)
-        flags, time, spark_state, _ = self._readback()
+        self._step1()
+        flags = int(self._obs_f[7, 0])
+        self._flags, self._t_servo = flags, int(self._obs_i[10, 0])
         if flags & N.F_MODE_ERROR:
             self._raise_mode_error()
         if flags & N.F_THERMAL_BREAK or broken_before:
@@ -114,23 +136,30 @@ class WireEDMEnv(EnvBase):
         obs = self._get_obs() if is_ctrl_step else None
         reward = self._calc_reward() if is_ctrl_step else 0.0
         info = {"wire_broken": bool(flags & N.F_BROKEN), "target_reached": bool(flags & N.F_TARGET),
-                "spark_state": spark_state, "time": time, "control_step": is_ctrl_step}
+                "spark_state": int(self._obs_i[9, 0]), "time": int(self._obs_i[8, 0]), "control_step": is_ctrl_step}
         return obs, reward, terminated, False, info
 
     def step_control(self, action, n_us: int | None = None):
-        """`n_us` (default servo_interval) microseconds in ONE kernel launch — the loop
+        """`n_us` (default servo_interval) microseconds in ONE call — the loop
         `for _ in range(1000): env.step(action)` of the reference's drivers (README.md:101-106)."""
-        n_us = self.servo_interval if n_us is None else int(n_us)
         self._stage(action)
-        self._engine.step(n_us)
-        flags, time, spark_state, _ = self._readback()
+        if n_us is None or int(n_us) == self.servo_interval:
+            self._stepN()
+        else:
+            self._engine.step_host(int(n_us))
+        flags = int(self._obs_f[7, 0])
+        self._flags, self._t_servo = flags, int(self._obs_i[10, 0])
         if flags & N.F_MODE_ERROR:
             self._raise_mode_error()
         info = {"wire_broken": bool(flags & N.F_BROKEN), "target_reached": bool(flags & N.F_TARGET),
-                "spark_state": spark_state, "time": time, "control_step": True}
+                "spark_state": int(self._obs_i[9, 0]), "time": int(self._obs_i[8, 0]), "control_step": True}
         return self._get_obs(), self._calc_reward(), bool(flags & N.F_DONE), False, info
 
     # ------------------------------------------------------------------ helpers
+    @property
+    def base_flow_rate(self) -> float:
+        return float(self.dielectric.params.base_flow_rate)
+
     def _get_obs(self):
         return {}          # placeholder in the reference too (wire_edm.py:181-183)
 

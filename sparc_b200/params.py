@@ -227,6 +227,7 @@ class SparcParams(C.Structure):
         ("density_times_cp", _D), ("plasma_efficiency", _D), ("base_convection_coefficient", _D),
         ("convection_velocity_factor", _D), ("convection_flow_enhancement", _D),
         ("critical_temperature_f32", _F), ("breaking_temperature_f32", _F),
+        ("cond_coeff_f32", _F), ("reserved1", _F),
         ("mech_dt", _D), ("damping_coeff", _D), ("stiffness_coeff", _D), ("omega_n", _D),
         ("max_acceleration", _D), ("max_jerk_dt", _D), ("max_speed", _D),
     ]
@@ -357,6 +358,7 @@ def derive_params(config: EnvironmentConfig, mechanics_control_mode: str = "posi
     # np.max(T) is float32; NumPy >= 2 compares it against the Python float rounded to float32
     p.critical_temperature_f32 = mat.melting_point * wr.critical_temp_threshold
     p.breaking_temperature_f32 = mat.breaking_temperature
+    p.cond_coeff_f32 = p.temp_update_factor * p.k_cond_coeff        # rounded to float32 by the ctypes field
 
     # mechanics.py:48-57
     p.mech_dt = config.dt * 1e-6

@@ -69,9 +69,19 @@ class BatchedSimulationLogger:
                 raise ValueError("LoggerConfig: 'filepath' for 'numpy' backend must be a string.")
             self.config["backend"].setdefault("compress", False)
 
+    def _engine(self):
+        eng = getattr(self.env, "engine", None)
+        return eng if eng is not None else self.env._engine      # the drop-in WireEDMEnv keeps it private
+
+    def _flow_scale(self) -> float:
+        """state.dielectric_flow_rate = flow_condition * base_flow_rate / 1e9 (dielectric.py:158)."""
+        return float(getattr(self.env, "base_flow_rate", 100.0)) / 1e9
+
     def _signal(self, name: str):
         """Device tensor of one EDMState attribute over the batch (a copy: the state is live)."""
-        eng = self.env.engine
+        eng = self._engine()
+        if name == "dielectric_flow_rate":
+            return eng["flow"] * self._flow_scale()
         if name == "wire_temperature":
             return eng.T.clone()
         if name in _SCALAR_MAP:
@@ -110,10 +120,34 @@ class BatchedSimulationLogger:
             kw["log_temperature_every"] = k
         return kw
 
+    def _collect_reference_style(self, state, info: Dict[str, Any]) -> None:
+        """`collect(state, info)` exactly as the reference's drivers call it after every 1-µs
+        `WireEDMEnv.step()` (utils/logger.py:118-160): every_step / control_step / interval counted in
+        calls; values read attribute by attribute from the state view, ndarrays copied."""
+        self.step_counter += 1
+        freq = self.config["log_frequency"]
+        if freq["type"] == "every_step":
+            should_log = True
+        elif freq["type"] == "control_step":
+            should_log = bool(info.get("control_step", False))
+        else:
+            should_log = self.step_counter % int(freq["value"]) == 0
+        if not should_log:
+            return
+        for name in self.config["signals_to_log"]:
+            if not hasattr(state, name):
+                print(f"Warning: No accessor found for signal '{name}'. Skipping.")
+                continue
+            value = getattr(state, name)
+            self.log_data[name].append(value.copy() if isinstance(value, np.ndarray) else value)
+
     def collect(self, info: Optional[Dict[str, Any]] = None, n_us: Optional[int] = None):
-        """Call after every `env.step()`.  `n_us` defaults to the env's control step."""
+        """Call after every `env.step()`.  `n_us` defaults to the env's control step.  The reference's
+        call `collect(env.state, info)` (drop-in `WireEDMEnv`, one µs per step) is accepted too."""
         if self.env is None:
             raise ValueError("BatchedSimulationLogger needs env_reference")
+        if info is not None and not isinstance(info, dict) and isinstance(n_us, dict):
+            return self._collect_reference_style(info, n_us)
         import torch
 
         n_us = int(self.env.servo_interval if n_us is None else n_us)
@@ -134,7 +168,9 @@ class BatchedSimulationLogger:
                 continue
             if slog is not None and name in self._SIGLOG:
                 rows = slog[self._SIGLOG[name]]    # kernel-sampled rows [n_samples, n_envs]
-                if name == "is_short_circuit":
+                if name == "dielectric_flow_rate":
+                    rows = rows * self._flow_scale()
+                elif name == "is_short_circuit":
                     rows = rows != 0
                 elif name in ("time", "spark_status", "time_in_critical_temp"):
                     rows = rows.to(dtype=torch.int32)
@@ -159,6 +195,9 @@ class BatchedSimulationLogger:
 
         numpy_data = {}
         for name, samples in self.log_data.items():
+            if not isinstance(samples[0], torch.Tensor):       # reference-style samples (drop-in env)
+                numpy_data[name] = np.array(samples)
+                continue
             arr = torch.stack(list(samples)).cpu().numpy()
             if arr.ndim >= 2 and arr.shape[1] == 1:
                 arr = arr[:, 0]                    # one env: the reference's (n_timesteps[, n_segments])
