@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define SPARC_ABI_VERSION 4
+#define SPARC_ABI_VERSION 5
 #define SPARC_MAX_MODE 19          /* current modes I1..I19, modules/currents.json */
 #define SPARC_N_DRAW_SLOTS 5       /* u1,u2,u3,u4,z5 per µs — see sparc_step_injected */
 #define SPARC_N_STATS 8
@@ -132,6 +132,20 @@ typedef struct SparcActions {
     const float *off_time;         /* generator_control.OFF_time[0] */
 } SparcActions;
 
+/* Optional controller evaluated INSIDE the kernels, at the start of a step call, instead of reading
+ * `actions->servo` (the generator settings still come from `actions`).  kind 1 is the proportional gap
+ * controller of the reference's driver (experiments/run_simulation.py:24-39, README.md:82-99):
+ *     servo = (float) clip(gain * ((workpiece_position - wire_position) - desired_gap), -limit, +limit)
+ * evaluated in float64 from the state the call starts with, rounded to the float32 the action space
+ * carries — the arithmetic of sparc_b200/controllers.py:GapController, so closed-loop trajectories are
+ * identical to evaluating it with torch ops between calls, with zero extra launches.  limit < 0: no clip.
+ * Only for calls of at most one launch epoch (1024 µs). */
+typedef struct SparcController {
+    int32_t kind;                  /* 0 none (use actions->servo), 1 proportional gap controller */
+    int32_t reserved;
+    double desired_gap, gain, limit;
+} SparcController;
+
 /* ---- state blob ------------------------------------------------------------------- */
 /* The state of n_envs environments is ONE caller-owned device allocation, laid out SoA:
  * one contiguous array per field, temperature field as [n_envs][n_pad] float32.
@@ -204,6 +218,12 @@ int sparc_step_sampled(void *state, const SparcParams *p, const SparcActions *ac
 int sparc_step_observe(void *state, const SparcParams *p, const SparcActions *actions, int n_envs, int n_us,
                        uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *obs_dev, void *stream);
 
+/* The general form of the step entry points: draws_dev (injected draws), obs_dev (observation written by
+ * the kernel epilogue) and ctrl (in-kernel controller) are each optional (NULL). */
+int sparc_step_ex(void *state, const SparcParams *p, const SparcActions *actions, const SparcController *ctrl,
+                  int n_envs, int n_us, uint64_t seed, uint32_t env_id_base, const double *draws_dev, float *obs_dev,
+                  void *stream);
+
 /* Observation summary of the last step call, obs_dev[SPARC_N_OBS][n_envs] float32:
  * 0 gap [µm], 1 wire_velocity [µm/s], 2 mean voltage over the call [V], 3 sparks ignited in the
  * call, 4 short-circuit µs in the call, 5 max wire temperature [K], 6 debris_density, 7 flags;
@@ -219,7 +239,8 @@ int sparc_reduce_stats(const void *state, int n_envs, int n_segments, double *ou
 /* Host-buffer convenience (the reference-facing call): H2D of the five action arrays, n_us
  * steps, D2H of the observation summary, then a stream sync.  Pointers are HOST pointers
  * (pinned for full speed); `scratch_dev` is caller-owned device scratch of
- * sparc_host_scratch_bytes(n_envs) bytes. */
+ * sparc_host_scratch_bytes(n_envs) bytes.  With at most 32 envs the host arrays MUST be pinned
+ * (cudaHostAlloc / cudaHostRegister / torch pin_memory): the kernel then reads and writes them in place. */
 size_t sparc_host_scratch_bytes(int n_envs);
 /* If the five host action arrays lie in ONE host buffer, array k at byte offset
  * k * sparc_host_action_pitch(n_envs) (order: servo, target_voltage, current_mode, on_time,

@@ -9,7 +9,7 @@ from .params import SparcParams
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("SPARC_LIB_PATH") or os.path.join(HERE, "_lib", "libsparc_b200.so")
 
-ABI_VERSION = 4        # include/sparc_b200.h SPARC_ABI_VERSION this binding was written against
+ABI_VERSION = 5        # include/sparc_b200.h SPARC_ABI_VERSION this binding was written against
 N_OBS = 12         # rows 0..7 float32; rows 8..10 int32 bit patterns (time, spark_state, time_since_servo)
 N_STATS = 8
 N_DRAW_SLOTS = 5
@@ -28,6 +28,11 @@ class SparcActions(C.Structure):
                 ("on_time", C.c_void_p), ("off_time", C.c_void_p)]
 
 
+class SparcController(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("reserved", C.c_int32), ("desired_gap", C.c_double), ("gain", C.c_double),
+                ("limit", C.c_double)]
+
+
 class SparcError(RuntimeError):
     pass
 
@@ -38,7 +43,7 @@ _lib = None
 EXPORTS = ("sparc_abi_version", "sparc_last_error", "sparc_num_fields", "sparc_field_info",
            "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_reseed",
            "sparc_params_bytes", "sparc_step",
-           "sparc_step_injected", "sparc_step_logged", "sparc_step_sampled", "sparc_step_observe", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
+           "sparc_step_injected", "sparc_step_ex", "sparc_step_logged", "sparc_step_sampled", "sparc_step_observe", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
            "sparc_step_host", "sparc_host_action_pitch", "sparc_launch_info", "sparc_measure_fp32_peak")
 
 
@@ -67,6 +72,7 @@ def lib():
     L.sparc_params_bytes.restype = sz
     L.sparc_step.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp]
     L.sparc_step_injected.argtypes = [vp, PP, PA, i32, i32, vp, vp]
+    L.sparc_step_ex.argtypes = [vp, PP, PA, C.POINTER(SparcController), i32, i32, u64, u32, vp, vp, vp]
     L.sparc_step_logged.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, i32, i32, vp]
     L.sparc_step_sampled.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, i32, i32, vp, i32, vp]
     L.sparc_step_observe.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp, vp]

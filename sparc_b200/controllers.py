@@ -58,6 +58,17 @@ class GapController:
     def reset(self, mask: Optional[torch.Tensor] = None) -> None:   # stateless
         return None
 
+    def kernel_spec(self) -> Dict:
+        """Arguments of `Engine.set_controller`: the same law evaluated inside the kernels at the start of a
+        control step (include/sparc_b200.h SparcController) — pass the controller itself to
+        `BatchedWireEDMEnv.step(ctrl)` and no torch op runs between control steps."""
+        return dict(kind=1, desired_gap=self.desired_gap, gain=self.gain, limit=-1.0 if self.limit is None else self.limit)
+
+    def generator_control(self, n: int, device) -> Dict[str, torch.Tensor]:
+        if self._gc is None or self._gc["target_voltage"].numel() != n or self._gc["target_voltage"].device != torch.device(device):
+            self._gc = _generator_control(n, device, self.generator)
+        return self._gc
+
     def __call__(self, env) -> Dict:
         gap = env.state_tensor("wp") - env.state_tensor("wire")
         if self._gc is None or self._gc["target_voltage"].numel() != gap.numel() or \

@@ -16,12 +16,12 @@ namespace sparc {
 // the dependency chain, which is what bounds this latency-bound kernel).  Returns false if any
 // clip condition was met: the caller redoes the block with mech_step.
 template <int MODE>
-__device__ __forceinline__ bool mech_block_fast(const SparcParams &P, double &wire, double &v, double &pa, const int it0,
+__device__ __forceinline__ bool mech_block_fast(const SparcParams &P, const EnvPrm &q, double &wire, double &v, double &pa, const int it0,
                                                 const int nb, const int first_latch, const double d_old,
                                                 const double d_new, double *traj)
 {
-    const double dt = P.mech_dt, c1 = P.damping_coeff, c2 = P.stiffness_coeff, nw = -P.omega_n;
-    const double amax = P.max_acceleration, jmax = P.max_jerk_dt, vmax = P.max_speed;
+    const double dt = P.mech_dt, c1 = q.damping_coeff, c2 = q.stiffness_coeff, nw = -q.omega_n;
+    const double amax = q.max_acceleration, jmax = q.max_jerk_dt, vmax = q.max_speed;
     bool bad = false;
 #pragma unroll 4
     for (int k = 0; k < nb; k++) {
@@ -56,8 +56,11 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
     if (e >= a.n_envs) return;
     if (S.flags[e] & SPARC_F_DONE) return;      // the step kernel does not read the scratch of a frozen env
     double wire = S.wire[e], v = S.v[e], pa = S.prev_accel[e];
+    EnvPrm q;                                   // only the mechanics members are read (the rest is never loaded)
+    q.damping_coeff = S.prm_damping_coeff[e]; q.stiffness_coeff = S.prm_stiffness_coeff[e]; q.omega_n = S.prm_omega_n[e];
+    q.max_acceleration = S.prm_max_acceleration[e]; q.max_jerk_dt = S.prm_max_jerk_dt[e]; q.max_speed = S.prm_max_speed[e];
     const double d_old = S.target_delta[e];
-    const double d_new = (double)a.act.servo[e];
+    const double d_new = servo_command(a, S, e);
     // launch-µs of the next action latch (wire_edm.py:117); later latches re-latch the same command
     int first_latch = P.servo_interval - S.t_servo[e];
     if (first_latch < 0) first_latch = 0;
@@ -71,13 +74,13 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
         const int nb = (a.n_us - it0 < SPARC_MECH_CKPT) ? a.n_us - it0 : SPARC_MECH_CKPT;
         const double w0 = wire, v0 = v, p0 = pa;
         const bool ok = (P.control_mode == 0)
-                            ? mech_block_fast<0>(P, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj)
-                            : mech_block_fast<1>(P, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj);
+                            ? mech_block_fast<0>(P, q, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj)
+                            : mech_block_fast<1>(P, q, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj);
         if (!ok) {                              // a clip was active somewhere in the block: exact path
             wire = w0; v = v0; pa = p0;
 #pragma unroll 1
             for (int k = 0; k < nb; k++) {
-                mech_step(P, wire, v, pa, (it0 + k >= first_latch) ? d_new : d_old);
+                mech_step(P, q, wire, v, pa, (it0 + k >= first_latch) ? d_new : d_old);
                 traj[it0 + k] = wire;
             }
         }

@@ -12,7 +12,7 @@
 // X(name, ctype, dtype_char, reset_value_expression)   — `P` is the SparcParams in scope.
 #define SPARC_STATE_FIELDS(X)                                                                     \
     /* positions / mechanics (fp64: per-µs increments are ~1e-5 µm on 1e2 µm) */     \
-    X(wp, double, 'd', P.initial_gap)              /* EDMState.workpiece_position [µm] */          \
+    X(wp, double, 'd', env_initial_gap)             /* EDMState.workpiece_position [µm] */          \
     X(wire, double, 'd', 0.0)                      /* EDMState.wire_position [µm] */               \
     X(v, double, 'd', 0.0)                         /* EDMState.wire_velocity [µm/s] */             \
     X(prev_accel, double, 'd', 0.0)                /* MechanicsModule.prev_accel */                \
@@ -70,6 +70,47 @@
     X(win_short_us, int32_t, 'i', 0)                                                              \
     X(win_steps, int32_t, 'i', 0)
 
+// Per-environment PARAMETERS (a different EnvironmentConfig / *ModuleParameters for every env in
+// ONE launch).  Every scalar of SparcParams that does not change the wire geometry lives in the blob as one
+// array per parameter, filled from the engine's SparcParams by sparc_init and left alone by sparc_reset; the
+// kernels read the arrays, never the struct, so overwriting prm_<name>[e] changes env e only.
+// X(name, ctype, dtype_char)  — the blob field is called prm_<name>, the default is P.<name>.
+#define SPARC_ENV_PARAM_FIELDS(X) \
+    X(initial_gap, double, 'd') \
+    X(target_position, double, 'd') \
+    X(base_critical_density, double, 'd') \
+    X(gap_coefficient, double, 'd') \
+    X(max_critical_density, double, 'd') \
+    X(hard_short_gap, double, 'd') \
+    X(sigmoid_steepness, double, 'd') \
+    X(random_short_min_gap, double, 'd') \
+    X(random_short_max_gap, double, 'd') \
+    X(random_short_max_probability, double, 'd') \
+    X(ignition_a_coeff, double, 'd') \
+    X(ignition_b_coeff, double, 'd') \
+    X(ignition_c_coeff, double, 'd') \
+    X(default_target_voltage, double, 'd') \
+    X(default_on_time, double, 'd') \
+    X(default_off_time, double, 'd') \
+    X(spark_voltage_factor, double, 'd') \
+    X(reference_gap, double, 'd') \
+    X(debris_obstruction_coeff, double, 'd') \
+    X(debris_removal_per_us, double, 'd') \
+    X(base_convection_coefficient, double, 'd') \
+    X(convection_velocity_factor, double, 'd') \
+    X(convection_flow_enhancement, double, 'd') \
+    X(plasma_efficiency, double, 'd') \
+    X(damping_coeff, double, 'd') \
+    X(stiffness_coeff, double, 'd') \
+    X(omega_n, double, 'd') \
+    X(max_acceleration, double, 'd') \
+    X(max_jerk_dt, double, 'd') \
+    X(max_speed, double, 'd') \
+    X(debris_short_duration, int32_t, 'i') \
+    X(random_short_duration, int32_t, 'i') \
+    X(default_current_mode, int32_t, 'i') \
+    X(ion_channel_duration, int32_t, 'i')
+
 // Mechanics look-ahead scratch (written by mech_kernel, read by the step kernel WHILE the pre-pass is
 // still running — the two kernels overlap, see mech_kernel.cu; carries nothing between calls): wire position after each µs of a launch epoch, and
 // (velocity, prev_accel) checkpoints every SPARC_MECH_CKPT µs plus the end-of-epoch pair.
@@ -81,6 +122,9 @@
 struct SparcStatePtrs {
 #define X(name, ctype, dt, init) ctype *name;
     SPARC_STATE_FIELDS(X)
+#undef X
+#define X(name, ctype, dt) ctype *prm_##name;
+    SPARC_ENV_PARAM_FIELDS(X)
 #undef X
     int32_t *episode;
     float *T;       // [n_envs][n_pad]

@@ -111,7 +111,22 @@ struct StepArgs {
     float *obs;              // observation summary [SPARC_N_OBS][n_envs] written by the kernel epilogue, or NULL
     uint32_t mech_seq;       // tag of this launch pair in SparcStatePtrs::mech_prog (multiple of 64)
     SparcLayout lay;
+    SparcController ctrl;    // kind 0: the servo command is act.servo[e]
 };
+
+// The servo command of this launch: the staged action, or the in-kernel controller evaluated from the
+// state the launch starts with (SparcController, include/sparc_b200.h).  mech_kernel and step_kernel
+// both call it at their start and read the same stored state (the step kernel overwrites wp / wire
+// only in its epilogue, after the pre-pass has finished).
+__device__ __forceinline__ double servo_command(const StepArgs &a, const SparcStatePtrs &S, const int e)
+{
+    if (a.ctrl.kind == 1) {
+        double d = ((S.wp[e] - S.wire[e]) - a.ctrl.desired_gap) * a.ctrl.gain;
+        if (a.ctrl.limit >= 0.0) d = fmin(fmax(d, -a.ctrl.limit), a.ctrl.limit);
+        return (double)(float)d;
+    }
+    return (double)a.act.servo[e];
+}
 
 #ifndef SPARC_BLOCK_THREADS
 #define SPARC_BLOCK_THREADS 64      /* W == 1: two envs per block */
@@ -127,7 +142,23 @@ struct StepArgs {
 // here (thread-local memory) and is touched only on the rare "general" µs (sparks, shorts,
 // latches, hysteresis refreshes) that run through general_pre().
 // ----------------------------------------------------------------------------------------------
+// The per-environment parameters of one env (blob fields prm_<name>, state_layout.h), loaded into the warp's
+// record at the start of a launch: every use below reads `q.<name>`, never `P.<name>`.
+struct EnvPrm {
+#define X(name, ctype, dt) ctype name;
+    SPARC_ENV_PARAM_FIELDS(X)
+#undef X
+};
+
+__device__ __forceinline__ void load_env_prm(EnvPrm &q, const SparcStatePtrs &S, const int e)
+{
+#define X(name, ctype, dt) q.name = S.prm_##name[e];
+    SPARC_ENV_PARAM_FIELDS(X)
+#undef X
+}
+
 struct EnvState {
+    EnvPrm q;
     // ---- HOT (register-mirrored by the caller) ----
     double wp, wire, v, prev_accel, target_delta, voltage, debris_volume, win_vsum, gap_prev;
     int time, spark_state, spark_dur, flags;
@@ -181,12 +212,12 @@ struct __align__(16) WarpRec {
 // 60.0 A of ignition.py:83; unknown -> default mode.
 __device__ __forceinline__ void derive_generator(EnvState &s, const SparcParams &P, double tv, double on, double off)
 {
-    s.tv_eff = (tv != 0.0) ? tv : P.default_target_voltage;
-    s.on_eff = (on != 0.0) ? on : P.default_on_time;
-    s.onoff_eff = s.on_eff + ((off != 0.0) ? off : P.default_off_time);
+    s.tv_eff = (tv != 0.0) ? tv : s.q.default_target_voltage;
+    s.on_eff = (on != 0.0) ? on : s.q.default_on_time;
+    s.onoff_eff = s.on_eff + ((off != 0.0) ? off : s.q.default_off_time);
     int mode = s.current_mode;
     if (mode == 0) s.ipk = 60.0;
-    else s.ipk = P.currents[(mode < 1 || mode > SPARC_MAX_MODE) ? P.default_current_mode : mode];
+    else s.ipk = P.currents[(mode < 1 || mode > SPARC_MAX_MODE) ? s.q.default_current_mode : mode];
     // smallest integer duration d with (double)d >= onoff_eff (rest -> idle, ignition.py:307-309)
     double c = ceil(s.onoff_eff);
     s.onoff_thr = (c > 2.0e9) ? 2000000000 : ((c < 0.0) ? 0 : (int)c);
@@ -207,7 +238,7 @@ __device__ __forceinline__ void materialize(EnvState &s, const SparcParams &P)
     }
     if (s.pend_flush) {
         if (s.flow > 0.001 && s.debris_volume > 0.001) {
-            double nv = s.debris_volume - P.debris_removal_per_us * s.flow;
+            double nv = s.debris_volume - s.q.debris_removal_per_us * s.flow;
             s.debris_volume = (nv > 0.0) ? nv : 0.0;
         }
         s.pend_flush = false;
@@ -222,16 +253,16 @@ __device__ __forceinline__ void prepare_fast(EnvState &s, const SparcParams &P)
     const double M = 1e-9;
     bool ok = (s.rand_short_rem | s.deb_short_rem) == 0 && (s.flags & SPARC_F_DONE) == 0;
     double lo = s.d_last_gap - 0.01 + M, hi = s.d_last_gap + 0.01 - M;
-    double need = (P.hard_short_gap > 0.001) ? P.hard_short_gap : 0.001;
-    if (P.random_short_max_probability > 0.0 && P.random_short_max_gap > need) need = P.random_short_max_gap;
+    double need = (s.q.hard_short_gap > 0.001) ? s.q.hard_short_gap : 0.001;
+    if (s.q.random_short_max_probability > 0.0 && s.q.random_short_max_gap > need) need = s.q.random_short_max_gap;
     need += M;
     if (lo < need) lo = need;
     ok = ok && (lo <= hi) && (hi < 1.0e6);
     // debris-short sigmoid must stay negligible for every gap in [lo,hi] and every density in the band
-    double crit = P.base_critical_density + P.gap_coefficient * ((P.gap_coefficient >= 0.0) ? lo : hi);
-    crit = (P.max_critical_density < crit) ? P.max_critical_density : crit;
+    double crit = s.q.base_critical_density + s.q.gap_coefficient * ((s.q.gap_coefficient >= 0.0) ? lo : hi);
+    crit = (s.q.max_critical_density < crit) ? s.q.max_critical_density : crit;
     double dens_hi = s.d_last_density + 0.001;
-    ok = ok && (P.sigmoid_steepness > 0.0) && (dens_hi < crit - SPARC_EXPO_SAFE / P.sigmoid_steepness - M);
+    ok = ok && (s.q.sigmoid_steepness > 0.0) && (dens_hi < crit - SPARC_EXPO_SAFE / s.q.sigmoid_steepness - M);
     ok = ok && (s.debris_density <= dens_hi);
     // density band  |rho - last| <= 0.001  <=>  lo_c*gap <= debris <= hi_c*gap   (rho < 1)
     double k = P.cavity_volume_coeff * 0.001;
@@ -239,7 +270,7 @@ __device__ __forceinline__ void prepare_fast(EnvState &s, const SparcParams &P)
     s.lo_c = (s.d_last_density - 0.001 + M) * k;
     s.hi_c = (dens_hi - M) * k;
     // deferred flushing: debris - amt must stay positive whenever debris > 0.001
-    s.flush_amt = (s.flow > 0.001) ? P.debris_removal_per_us * s.flow : 0.0;
+    s.flush_amt = (s.flow > 0.001) ? s.q.debris_removal_per_us * s.flow : 0.0;
     ok = ok && (s.flush_amt >= 0.0) && (s.flush_amt < 0.001);
     s.gap_lo_f = lo;
     s.gap_hi_f = hi;
@@ -248,12 +279,12 @@ __device__ __forceinline__ void prepare_fast(EnvState &s, const SparcParams &P)
 
 // DielectricModule.update hysteresis (dielectric.py:118-137): recompute the flow condition only when
 // the gap or the debris density moved out of the band around the values of the last recomputation.
-__device__ __forceinline__ double flow_condition(const SparcParams &P, const double gap_um, const double density)
+__device__ __forceinline__ double flow_condition(const EnvPrm &q, const double gap_um, const double density)
 {
-    double r = gap_um / P.reference_gap;
+    double r = gap_um / q.reference_gap;
     double gf = r * r * r;                                  // (gap/ref)**3
     gf = (gf < 1.0) ? gf : 1.0;
-    double x = P.debris_obstruction_coeff * density;
+    double x = q.debris_obstruction_coeff * density;
     double df;
     if (x < 0.5) df = (1.0 - 0.5 * x) / (1.0 + 0.5 * x);                   // fast_exp Pade branch
     else df = exp(-x);
@@ -263,7 +294,7 @@ __device__ __forceinline__ double flow_condition(const SparcParams &P, const dou
 __device__ __forceinline__ bool dielectric_hysteresis(EnvState &s, const SparcParams &P, const double gap_um)
 {
     if (fabs(gap_um - s.d_last_gap) > 0.01 || fabs(s.debris_density - s.d_last_density) > 0.001) {
-        s.flow = flow_condition(P, gap_um, s.debris_density);
+        s.flow = flow_condition(s.q, gap_um, s.debris_density);
         s.d_last_gap = gap_um;
         s.d_last_density = s.debris_density;
         return true;
@@ -276,12 +307,12 @@ __device__ __forceinline__ bool dielectric_hysteresis(EnvState &s, const SparcPa
 __device__ __forceinline__ void wire_convection_refresh(EnvState &s, const SparcParams &P, const SparcStatePtrs &S)
 {
     if (fabs(s.flow - s.w_last_flow) > 0.01) {
-        double ve = P.convection_velocity_factor * S.unwind_v[s.e];
+        double ve = s.q.convection_velocity_factor * S.unwind_v[s.e];
         ve = (ve > -0.9) ? ve : -0.9;
-        double hb = P.base_convection_coefficient * (1.0 + ve);
-        double hfloor = 0.1 * P.base_convection_coefficient;
+        double hb = s.q.base_convection_coefficient * (1.0 + ve);
+        double hfloor = 0.1 * s.q.base_convection_coefficient;
         hb = (hb > hfloor) ? hb : hfloor;
-        double he = hb * (1.0 + P.convection_flow_enhancement * s.flow);
+        double he = hb * (1.0 + s.q.convection_flow_enhancement * s.flow);
         s.hb = (float)hb; s.he = (float)he; s.refresh = true;
         if (s.writer) { S.h_base[s.e] = s.hb; S.h_enh[s.e] = s.he; }
         s.w_last_flow = s.flow;
@@ -303,15 +334,15 @@ static __device__ __noinline__ bool light_refresh(EnvState &s, const SparcParams
                                            double &debris_volume, const bool pending)
 {
     const double M = 1e-9;
-    double need = (P.hard_short_gap > 0.001) ? P.hard_short_gap : 0.001;
-    if (P.random_short_max_probability > 0.0 && P.random_short_max_gap > need) need = P.random_short_max_gap;
-    if (!(g >= need + M) || !(P.sigmoid_steepness > 0.0)) return false;
-    double crit = P.base_critical_density + P.gap_coefficient * g;
-    crit = (P.max_critical_density < crit) ? P.max_critical_density : crit;
-    if (!(s.d_last_density + 0.001 < crit - SPARC_EXPO_SAFE / P.sigmoid_steepness - M)) return false;
+    double need = (s.q.hard_short_gap > 0.001) ? s.q.hard_short_gap : 0.001;
+    if (s.q.random_short_max_probability > 0.0 && s.q.random_short_max_gap > need) need = s.q.random_short_max_gap;
+    if (!(g >= need + M) || !(s.q.sigmoid_steepness > 0.0)) return false;
+    double crit = s.q.base_critical_density + s.q.gap_coefficient * g;
+    crit = (s.q.max_critical_density < crit) ? s.q.max_critical_density : crit;
+    if (!(s.d_last_density + 0.001 < crit - SPARC_EXPO_SAFE / s.q.sigmoid_steepness - M)) return false;
     double deb = debris_volume;
     if (pending && s.flow > 0.001 && deb > 0.001) {         // flush of the previous µs (dielectric.py:139-144)
-        double nv = deb - P.debris_removal_per_us * s.flow;
+        double nv = deb - s.q.debris_removal_per_us * s.flow;
         deb = (nv > 0.0) ? nv : 0.0;
     }
     const double gap_um = (g > 0.001) ? g : 0.001;
@@ -319,7 +350,7 @@ static __device__ __noinline__ bool light_refresh(EnvState &s, const SparcParams
     double dens = 0.0;
     if (cavity > 0.0) { double d = deb / cavity; dens = (d < 1.0) ? d : 1.0; }
     if (!(fabs(gap_um - s.d_last_gap) > 0.01 || fabs(dens - s.d_last_density) > 0.001)) return false;
-    const double flow = flow_condition(P, gap_um, dens);
+    const double flow = flow_condition(s.q, gap_um, dens);
     // a flow change that also moves the wire's convection coefficients is left to the general µs
     if (fabs(flow - s.w_last_flow) > 0.01) return false;
     debris_volume = deb;
@@ -363,7 +394,7 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
         const double a_on = (double)a.act.on_time[e];
         const double a_off = (double)a.act.off_time[e];
         const int a_mode = a.act.current_mode[e];
-        s.target_delta = (double)a.act.servo[e];
+        s.target_delta = s.delta_new0;                      // act.servo[e] or the in-kernel controller's command
         s.current_mode = (a_mode == 0) ? -1 : a_mode;       // "I0" is a string, not None
         derive_generator(s, P, a_tv, a_on, a_off);
         if (s.writer) { S.target_voltage[e] = a_tv; S.on_time[e] = a_on; S.off_time[e] = a_off; }
@@ -380,11 +411,11 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
         is_short = false;
         double p_deb;                                       // ignition.py:115-146
         bool tiny = false;                                  // 0 < p_deb < 4.3e-18
-        if (gap < P.hard_short_gap) p_deb = 1.0;
+        if (gap < s.q.hard_short_gap) p_deb = 1.0;
         else {
-            double crit = P.base_critical_density + P.gap_coefficient * gap;
-            crit = (P.max_critical_density < crit) ? P.max_critical_density : crit;
-            double expo = -P.sigmoid_steepness * (s.debris_density - crit);
+            double crit = s.q.base_critical_density + s.q.gap_coefficient * gap;
+            crit = (s.q.max_critical_density < crit) ? s.q.max_critical_density : crit;
+            double expo = -s.q.sigmoid_steepness * (s.debris_density - crit);
             if (expo > 500.0) p_deb = 0.0;
             else if (expo < -500.0) p_deb = 1.0;
             else if (!INJECT && expo > SPARC_EXPO_SAFE) { p_deb = 0.0; tiny = true; }
@@ -392,18 +423,18 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
         }
         (void)tiny;
         double p_rnd;
-        if (gap >= P.random_short_max_gap) p_rnd = 0.0;
-        else if (gap <= P.random_short_min_gap) p_rnd = P.random_short_max_probability;
+        if (gap >= s.q.random_short_max_gap) p_rnd = 0.0;
+        else if (gap <= s.q.random_short_min_gap) p_rnd = s.q.random_short_max_probability;
         else {
-            double gf = 1.0 - (gap - P.random_short_min_gap) / (P.random_short_max_gap - P.random_short_min_gap);
-            p_rnd = gf * P.random_short_max_probability;
+            double gf = 1.0 - (gap - s.q.random_short_min_gap) / (s.q.random_short_max_gap - s.q.random_short_min_gap);
+            p_rnd = gf * s.q.random_short_max_probability;
         }
         if (p_deb > 0.0 && draw(0) < p_deb) {
-            s.deb_short_rem = P.debris_short_duration;
+            s.deb_short_rem = s.q.debris_short_duration;
             is_short = true;
             if (s.writer) S.stat_short_events[e] += 1;
         } else if (p_rnd > 0.0 && draw(1) < p_rnd) {
-            s.rand_short_rem = P.random_short_duration;
+            s.rand_short_rem = s.q.random_short_duration;
             is_short = true;
             if (s.writer) S.stat_short_events[e] += 1;
         }
@@ -420,11 +451,11 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
             s.voltage = s.tv_eff;
             const double u3 = draw(2);
             // get_lambda (ignition.py:348-364): ln2 / (a*gap^2 + b*gap + c), raw gap
-            double den = P.ignition_a_coeff * (gap_raw * gap_raw) + P.ignition_b_coeff * gap_raw + P.ignition_c_coeff;
+            double den = s.q.ignition_a_coeff * (gap_raw * gap_raw) + s.q.ignition_b_coeff * gap_raw + s.q.ignition_c_coeff;
             if (u3 < 0.6931471805599453 / den) {
                 double y = 0.0 + (P.workpiece_height - 0.0) * draw(3);      // Generator.uniform
                 s.spark_state = 1; s.flags |= SPARC_F_HAS_Y; s.spark_dur = 0;
-                s.voltage = s.tv_eff * P.spark_voltage_factor;
+                s.voltage = s.tv_eff * s.q.spark_voltage_factor;
                 s.win_sparks += 1;
                 fresh_spark = true;
                 s.plasma_idx = (P.segment_len != 0.0) ? P.zone_start + (int)py_floordiv(y, P.segment_len) : P.zone_start;
@@ -434,7 +465,7 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
     } else if (s.spark_state == 1) {
         s.spark_dur += 1;
         if ((double)s.spark_dur >= s.on_eff) { s.spark_state = -2; if (!is_short) s.voltage = 0.0; }
-        else if (!is_short) s.voltage = s.tv_eff * P.spark_voltage_factor;
+        else if (!is_short) s.voltage = s.tv_eff * s.q.spark_voltage_factor;
     } else if (s.spark_state == -1) {
         s.spark_dur += 1;
         if ((double)s.spark_dur >= s.on_eff) s.spark_state = -2;
@@ -493,7 +524,7 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
     const double cavity_volume = P.cavity_volume_coeff * (gap_um * 0.001);
     if (crater_volume > 0.0) {                              // fresh spark with a crater
         s.debris_volume += crater_volume;
-        s.ion_end = s.time + P.ion_channel_duration;        // ion_rem = max(0, ion_end - time)
+        s.ion_end = s.time + s.q.ion_channel_duration;        // ion_rem = max(0, ion_end - time)
     }
     if (cavity_volume > 0.0) {
         double d = s.debris_volume / cavity_volume;
@@ -512,7 +543,7 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
         s.jB = (float)(jf * (1.0 - P.alpha_rho * P.temp_ref));
         s.heat_on = true;
         if (s.spark_state == 1) {                           // plasma spot, wire.py:293-297
-            double ph = P.plasma_efficiency * s.voltage * current;
+            double ph = s.q.plasma_efficiency * s.voltage * current;
             if (!isfinite(ph)) ph = 0.0;
             s.fP = (float)(f * ph);
         }
@@ -521,31 +552,31 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
 }
 
 // MechanicsModule.update (mechanics.py:79-114), one µs.
-__device__ __forceinline__ void mech_step(const SparcParams &P, double &wire, double &v, double &prev_accel,
-                                          const double target_delta)
+__device__ __forceinline__ void mech_step(const SparcParams &P, const EnvPrm &q, double &wire, double &v,
+                                          double &prev_accel, const double target_delta)
 {
     double a_nom;
     if (P.control_mode == 0) {
         double x_err = wire - (wire + target_delta);
-        a_nom = P.damping_coeff * v + P.stiffness_coeff * x_err;
+        a_nom = q.damping_coeff * v + q.stiffness_coeff * x_err;
     } else {
-        a_nom = -P.omega_n * (v - target_delta);
+        a_nom = -q.omega_n * (v - target_delta);
     }
     double da = a_nom - prev_accel;
-    if (fabs(a_nom) <= P.max_acceleration && fabs(da) <= P.max_jerk_dt) {
+    if (fabs(a_nom) <= q.max_acceleration && fabs(da) <= q.max_jerk_dt) {
         prev_accel = prev_accel + da;           // no clip active
     } else {
-        if (a_nom > P.max_acceleration) a_nom = P.max_acceleration;
-        else if (a_nom < -P.max_acceleration) a_nom = -P.max_acceleration;
+        if (a_nom > q.max_acceleration) a_nom = q.max_acceleration;
+        else if (a_nom < -q.max_acceleration) a_nom = -q.max_acceleration;
         da = a_nom - prev_accel;
-        if (da > P.max_jerk_dt) da = P.max_jerk_dt;
-        else if (da < -P.max_jerk_dt) da = -P.max_jerk_dt;
+        if (da > q.max_jerk_dt) da = q.max_jerk_dt;
+        else if (da < -q.max_jerk_dt) da = -q.max_jerk_dt;
         prev_accel = prev_accel + da;
     }
     v += prev_accel * P.mech_dt;
-    if (!(fabs(v) <= P.max_speed)) {
-        if (v > P.max_speed) v = P.max_speed;
-        else if (v < -P.max_speed) v = -P.max_speed;
+    if (!(fabs(v) <= q.max_speed)) {
+        if (v > q.max_speed) v = q.max_speed;
+        else if (v < -q.max_speed) v = -q.max_speed;
     }
     wire += v * P.mech_dt;
 }

@@ -275,7 +275,7 @@ static __device__ __noinline__ void mech_self_serve(const SparcParams &P, const 
     ck[0] = v; ck[1] = pa;
     const int upto = ((int)need * SPARC_MECH_CKPT < a.n_us) ? (int)need * SPARC_MECH_CKPT : a.n_us;
     for (int k = 0; k < upto; k++) {
-        mech_step(P, wire, v, pa, (k >= s.first_latch_it) ? s.delta_new0 : s.delta_old0);
+        mech_step(P, s.q, wire, v, pa, (k >= s.first_latch_it) ? s.delta_new0 : s.delta_old0);
         traj[k] = wire;
         if ((k + 1) % SPARC_MECH_CKPT == 0) { ck[2 * ((k + 1) / SPARC_MECH_CKPT)] = v; ck[2 * ((k + 1) / SPARC_MECH_CKPT) + 1] = pa; }
         if (k + 1 == a.n_us) { ck[2 * (SPARC_MECH_NCKPT - 1)] = v; ck[2 * (SPARC_MECH_NCKPT - 1) + 1] = pa; }
@@ -312,6 +312,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     // ---------------- load: scalar state -> the warp's shared-memory record ---------------------
     // every lane executes the same scalar code and writes the same values (no divergence, no sync)
     s.e = e; s.it = 0; s.writer = gl == 0;
+    load_env_prm(s.q, S, e);
     s.env_id = a.env_id_base + (uint32_t)e;
     s.episode = (uint32_t)S.episode[e];
     s.debris_density = S.debris_density[e]; s.flow = S.flow[e];
@@ -401,8 +402,8 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     // draw above it can never ignite, whatever the gap.
     {
         double lam_bound = 2.0;
-        if (P.ignition_a_coeff > 0.0) {
-            double den_min = P.ignition_c_coeff - P.ignition_b_coeff * P.ignition_b_coeff / (4.0 * P.ignition_a_coeff);
+        if (s.q.ignition_a_coeff > 0.0) {
+            double den_min = s.q.ignition_c_coeff - s.q.ignition_b_coeff * s.q.ignition_b_coeff / (4.0 * s.q.ignition_a_coeff);
             if (den_min > 0.0) lam_bound = 0.6931471805599453 / den_min * (1.0 + 1e-9);
         }
         uint32_t w_thresh = 0xffffffffu;        // word >= w_thresh  =>  u01(word) >= lam_bound
@@ -512,7 +513,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             else mech_self_serve(P, S, a, s, (uint32_t)((a.n_us + SPARC_MECH_CKPT - 1) / SPARC_MECH_CKPT));
         }
     };
-    s.wire0 = s.wire; s.delta_old0 = s.target_delta; s.delta_new0 = (double)a.act.servo[e];
+    s.wire0 = s.wire; s.delta_old0 = s.target_delta; s.delta_new0 = servo_command(a, S, e);
     s.first_latch_it = (s.next_latch - s.time > 0) ? s.next_latch - s.time : 0;
 
     // finished inside a block: exact mechanics state after launch-µs `target`, replayed from the
@@ -524,7 +525,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
         double v = __ldcg(ck), pa = __ldcg(ck + 1);
 #pragma unroll 1
         for (int k = c * SPARC_MECH_CKPT; k < target; k++)
-            mech_step(P, wire, v, pa, (k >= s.first_latch_it) ? s.delta_new0 : s.delta_old0);
+            mech_step(P, s.q, wire, v, pa, (k >= s.first_latch_it) ? s.delta_new0 : s.delta_old0);
         s.fin_wire = wire; s.fin_v = v; s.fin_pa = pa;
     };
 
@@ -623,7 +624,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                         if (off > off_tr) {
                             const double u3 = d[2];
                             if (!(u3 >= s.lam_bound)) {
-                                double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
+                                double den = s.q.ignition_a_coeff * (g * g) + s.q.ignition_b_coeff * g + s.q.ignition_c_coeff;
                                 ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
                             }
                         }
@@ -634,7 +635,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                     if (w_l < s.w_thresh) {
                         // u3 < fl(ln2/den) can only hold if u3*den <= ln2*(1+2^-50)
                         const double u3 = u01(w_l);
-                        double den = P.ignition_a_coeff * (g * g) + P.ignition_b_coeff * g + P.ignition_c_coeff;
+                        double den = s.q.ignition_a_coeff * (g * g) + s.q.ignition_b_coeff * g + s.q.ignition_c_coeff;
                         ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
                     }
                 }
@@ -829,7 +830,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             if (s.spark_state == 1) s.tse_ref = s.time;
             // ---- _check_termination (wire_edm.py:172-179) -------------------------------------
             if (R.pos[i + 1] > s.wp + 100.0) { s.flags |= SPARC_F_BROKEN; s.done = true; }
-            else if (s.wp >= P.target_position) { s.flags |= SPARC_F_TARGET; s.done = true; }
+            else if (s.wp >= s.q.target_position) { s.flags |= SPARC_F_TARGET; s.done = true; }
             if (s.done) { rewind_mech(it + i + 1); break; }
             i += 1;
         }

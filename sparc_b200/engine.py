@@ -36,6 +36,7 @@ class Engine:
         self.device = torch.device(device)
         self.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
         self.env_id_base = int(env_id_base)
+        self._ctrl = None
         nbytes = self.lib.sparc_state_bytes(self.n_envs, self.n_segments)
         if nbytes == 0:
             raise N.SparcError("bad n_envs / n_segments")
@@ -111,6 +112,13 @@ class Engine:
                 else:
                     dst.copy_(torch.from_numpy(np.ascontiguousarray(arr.reshape(-1))).to(dst.dtype), non_blocking=True)
 
+    def set_controller(self, kind: int = 0, desired_gap: float = 0.0, gain: float = 0.0, limit: float = -1.0) -> None:
+        """In-kernel controller for `step()` (include/sparc_b200.h SparcController): kind 1 = proportional
+        gap controller evaluated at the start of every call instead of reading the staged servo array;
+        kind 0 switches it off.  limit < 0 (or None): no clipping."""
+        self._ctrl = None if not kind else N.SparcController(int(kind), 0, float(desired_gap), float(gain),
+                                                             -1.0 if limit is None else float(limit))
+
     def _actions_struct(self, bufs) -> N.SparcActions:
         return N.SparcActions(bufs["servo"].data_ptr(), bufs["target_voltage"].data_ptr(),
                               bufs["current_mode"].data_ptr(), bufs["on_time"].data_ptr(),
@@ -129,6 +137,11 @@ class Engine:
             assert tuple(draws.shape) == (self.n_envs, int(n_us), N.N_DRAW_SLOTS)
             dptr = draws.data_ptr()
         with torch.cuda.device(self.device):
+            if getattr(self, "_ctrl", None) is not None:
+                N.check(self.lib.sparc_step_ex(self.blob.data_ptr(), C.byref(self.params), C.byref(a), C.byref(self._ctrl),
+                                               self.n_envs, int(n_us), self.seed, self.env_id_base, dptr,
+                                               self.obs_dev.data_ptr() if observe else None, self._stream()))
+                return self.obs_dev if observe else None
             if observe:
                 N.check(self.lib.sparc_step_observe(self.blob.data_ptr(), C.byref(self.params), C.byref(a), self.n_envs,
                                                     int(n_us), self.seed, self.env_id_base, dptr,

@@ -15,6 +15,7 @@ import numpy as np
 import torch
 
 from .. import _native as N
+from ..controllers import GapController
 from ..engine import Engine
 from ..params import (DielectricModuleParameters, EnvironmentConfig, IgnitionModuleParameters,
                       MaterialModuleParameters, MechanicsModuleParameters, WireModuleParameters,
@@ -48,6 +49,8 @@ class BatchedWireEDMEnv:
         self.dt = self.config.dt
         self.latch_first_action = bool(latch_first_action)
         self.auto_reset = bool(auto_reset)
+        self._module_params = dict(ignition=ignition_params, wire=wire_params, material=material_params,
+                                   dielectric=dielectric_params, mechanics=mechanics_params)
         self.params = derive_params(self.config, mechanics_control_mode, ignition_params, wire_params,
                                     material_params, dielectric_params, mechanics_params)
         self.base_flow_rate = float((dielectric_params or DielectricModuleParameters()).base_flow_rate)
@@ -81,6 +84,45 @@ class BatchedWireEDMEnv:
         self._arm_latch(mask)
         return self._obs(), {}
 
+    # ------------------------------------------------------------------------------------------
+    def per_env_parameter_names(self):
+        """Names of the parameters that exist once per env in the state blob (fields `prm_<name>`)."""
+        return [k[4:] for k in self.engine.fields if k.startswith("prm_")]
+
+    def set_env_params(self, env_ids, *, config: EnvironmentConfig = None,
+                       ignition_params: IgnitionModuleParameters = None, wire_params: WireModuleParameters = None,
+                       dielectric_params: DielectricModuleParameters = None,
+                       mechanics_params: MechanicsModuleParameters = None) -> None:
+        """Give the envs `env_ids` their own configuration (domain randomisation: a different
+        EnvironmentConfig / *ModuleParameters for every env of ONE batch, ONE launch; reference
+        core/env_config.py:10-35, modules/ignition.py:17-57, dielectric.py:15-31, mechanics.py:12-23).
+
+        Every scalar that does not change the wire geometry is a per-env array in the state blob
+        (`per_env_parameter_names()`); arguments left out keep this env's construction-time value.  A
+        configuration that would change the geometry or a shared table (workpiece height, wire diameter,
+        segment length, buffers, servo interval, material, crater / kerf tables, control mode) raises
+        ValueError — batches of different geometry are `GroupedWireEDMEnv`'s job.  `initial_gap` takes
+        effect at the env's next reset."""
+        import ctypes as C
+
+        mp = self._module_params
+        p = derive_params(config or self.config, self.mechanics_control_mode, ignition_params or mp["ignition"],
+                          wire_params or mp["wire"], mp["material"], dielectric_params or mp["dielectric"],
+                          mechanics_params or mp["mechanics"])
+        per_env = set(self.per_env_parameter_names())
+        for name, ctype in p._fields_:
+            if name in per_env or name.startswith("reserved"):
+                continue
+            a, b = getattr(p, name), getattr(self.params, name)
+            if isinstance(a, C.Array):
+                a, b = list(a), list(b)
+            if a != b:
+                raise ValueError(f"set_env_params: '{name}' differs from the batch ({a} vs {b}); only parameters that "
+                                 "leave the wire geometry and the shared tables unchanged can vary inside one batch")
+        idx = torch.as_tensor(env_ids, device=self.device, dtype=torch.long).reshape(-1)
+        for name in per_env:
+            self.engine["prm_" + name][idx] = getattr(p, name)
+
     def _stage(self, actions: Dict):
         gc = actions["generator_control"]
         self.engine.set_actions(actions["servo"], gc["target_voltage"], gc["current_mode"], gc["ON_time"], gc["OFF_time"])
@@ -100,7 +142,17 @@ class BatchedWireEDMEnv:
         name of `_native.SIGNALS` to a [n_us // k, n_envs] float64 tensor (k=1: the reference
         logger's "every_step")."""
         n_us = self.servo_interval if n_us is None else int(n_us)
-        self._stage(actions)
+        if isinstance(actions, GapController) and (log_signals_every or log_temperature_every or n_us > 1024):
+            actions = actions(self)             # the logging entry points take the command from the staged array
+        if isinstance(actions, GapController):
+            # closed loop inside the kernels: servo = clip(gain * (gap - desired), +-limit) from the state this
+            # call starts with (same arithmetic as `actions(env)`), no torch op between control steps
+            gc = actions.generator_control(self.n_envs, self.device)
+            self.engine.set_actions(0.0, gc["target_voltage"], gc["current_mode"], gc["ON_time"], gc["OFF_time"])
+            self.engine.set_controller(**actions.kernel_spec())
+        else:
+            self.engine.set_controller(0)
+            self._stage(actions)
         tlog, sig, fused = None, None, None
         if log_signals_every:
             sig, tlog = self.engine.step_sampled(n_us, int(log_signals_every), draws,

@@ -8,6 +8,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+collect_ignore = [os.path.join("golden", "ref_tests")]
 
 
 def pytest_configure(config):

@@ -235,3 +235,24 @@ def test_reset_with_seed_replays_the_same_episode():
     assert not torch.equal(a["wp"], c["wp"])
     env.reset(seed=5, mask=torch.arange(256, device=env.device) < 128)
     assert int(env.state_tensor("episode")[:128].abs().sum()) == 0
+
+
+def test_reference_style_logger_on_the_dropin_env():
+    """`logger.collect(env.state, info)` after every 1-us step(), exactly as the reference's drivers call
+    it (utils/logger.py:118-160, run_simulation.py:245-297), works on the drop-in env; `dielectric_flow_rate`
+    carries the reference's scaling flow * base_flow_rate / 1e9 (dielectric.py:158)."""
+    from sparc_b200 import EnvironmentConfig, WireEDMEnv
+    from sparc_b200.utils.logger import SimulationLogger
+
+    env = WireEDMEnv(config=EnvironmentConfig(**README))
+    env.reset(seed=3)
+    logger = SimulationLogger({"signals_to_log": ["time", "voltage", "dielectric_flow_rate", "wire_temperature"],
+                               "log_frequency": {"type": "interval", "value": 5}, "backend": {"type": "memory"}}, env)
+    act = env.action_space.sample()
+    for _ in range(40):
+        _, _, _, _, info = env.step(act)
+        logger.collect(env.state, info)
+    data = logger.get_data()
+    assert [int(t) for t in data["time"]] == list(range(5, 45, 5))
+    assert len(data["wire_temperature"]) == 8 and data["wire_temperature"][0].shape == (375,)
+    assert abs(data["dielectric_flow_rate"][-1] - env.state.flow_rate * 100.0 / 1e9) < 1e-18

@@ -80,7 +80,8 @@ def test_cfg2_philox_at_baseline_batch_sizes(n_envs):
     print(f"\n[cfg2 x{n_envs}] {len(envs)} sampled envs match the oracle over 20 control steps; max |dT| {worst:.3e} K")
 
 
-def test_cfg3_closed_loop_philox_16384_envs():
+@pytest.mark.parametrize("in_kernel", [False, True])
+def test_cfg3_closed_loop_philox_16384_envs(in_kernel):
     """BASELINE configs[2]: 16384 envs, position mode, P gap controller (25 um, limit 1) closed on the
     device; every sampled oracle is driven by the reference's controller arithmetic
     (experiments/run_simulation.py:27-39) from its own state."""
@@ -98,7 +99,7 @@ def test_cfg3_closed_loop_philox_16384_envs():
     oracles = {e: O.OracleEnv(**CS.oracle_overrides(case)) for e in envs}
     worst = 0.0
     for k in range(STEPS):
-        env.step(ctrl(env))
+        env.step(ctrl if in_kernel else ctrl(env))
         for e in envs:
             f, _ = oracles[e].record()
             servo = np.float32(np.clip((f[0] - f[1] - 25.0) * 0.1, -1.0, 1.0))
@@ -168,3 +169,76 @@ def test_overlapped_and_serial_prepass_agree_bit_for_bit():
     a = _state_hash({})
     b = _state_hash({"SPARC_NO_PDL": "1"})
     assert a == b
+
+
+def test_per_env_parameters_in_one_launch_match_their_own_oracles():
+    """SURVEY §8f-3 / VERDICT r1 missing #1: 64 envs with 64 DIFFERENT parameter sets (initial gap, target
+    distance, ignition curve and short-circuit model, dielectric flushing, servo dynamics, convection) in ONE
+    batch and ONE launch per control step; every env is compared with its own OracleEnv built from the same
+    overrides, draws injected — against the oracle, not against another CUDA run."""
+    import torch
+    from sparc_b200 import (BatchedWireEDMEnv, DielectricModuleParameters, EnvironmentConfig, IgnitionModuleParameters,
+                            MechanicsModuleParameters, WireModuleParameters)
+
+    E, STEPS, SI = 64, 12, 1000
+    rng = np.random.default_rng(2026)
+    env = BatchedWireEDMEnv(E, config=EnvironmentConfig(**CS.README_CFG), mechanics_control_mode="position",
+                            latch_first_action=False)
+    sets = []
+    for e in range(E):
+        cfg = dict(CS.README_CFG, initial_gap=float(rng.uniform(8.0, 60.0)),
+                   target_cutting_distance=float(rng.choice([800.0, 12.0 + rng.uniform(0, 50.0)])))
+        ign = dict(ignition_a_coeff=float(rng.uniform(0.3, 0.7)), ignition_b_coeff=float(rng.uniform(-4.2, -3.0)),
+                   ignition_c_coeff=float(rng.uniform(12.0, 17.0)), base_critical_density=float(rng.uniform(0.05, 0.4)),
+                   gap_coefficient=float(rng.uniform(0.001, 0.03)), sigmoid_steepness=float(rng.uniform(200.0, 600.0)),
+                   random_short_max_probability=float(rng.choice([0.0, 0.001, 0.004])),
+                   debris_short_duration=int(rng.integers(20, 80)), spark_voltage_factor=float(rng.uniform(0.2, 0.4)))
+        die = dict(debris_removal_efficiency=float(rng.uniform(0.0005, 0.02)), reference_gap=float(rng.uniform(15.0, 35.0)),
+                   debris_obstruction_coeff=float(rng.uniform(0.5, 2.0)), ion_channel_duration=int(rng.integers(3, 9)))
+        mec = dict(omega_n=float(rng.uniform(150.0, 320.0)), zeta=float(rng.uniform(0.2, 0.9)),
+                   max_speed=float(rng.choice([3.0e4, 2.0e2])))
+        wir = dict(base_convection_coefficient=float(rng.uniform(8000.0, 20000.0)), plasma_efficiency=float(rng.uniform(0.05, 0.2)))
+        sets.append((cfg, ign, die, mec, wir))
+        env.set_env_params([e], config=EnvironmentConfig(**cfg), ignition_params=IgnitionModuleParameters(**ign),
+                           dielectric_params=DielectricModuleParameters(**die), mechanics_params=MechanicsModuleParameters(**mec),
+                           wire_params=WireModuleParameters(**wir))
+    env.reset()
+    np.testing.assert_allclose(env.state_tensor("wp").cpu().numpy(), [s[0]["initial_gap"] for s in sets])
+    oracles = []
+    for cfg, ign, die, mec, wir in sets:
+        case = {"config": cfg, "mode": "position", "ignition": ign, "dielectric": die, "mechanics": mec, "wire": wir}
+        oracles.append(O.OracleEnv(**CS.oracle_overrides(case)))
+    g = np.random.Generator(np.random.Philox(key=99))
+    tape = np.ascontiguousarray(np.concatenate([g.random((E, STEPS * SI, 4)), g.standard_normal((E, STEPS * SI, 1))], axis=2))
+    tape_dev = torch.from_numpy(tape).cuda()
+    servo = rng.uniform(-0.3, 0.6, size=E).astype(np.float32)
+    modes = rng.choice([3, 5, 7, 9, 13], size=E).astype(np.int32)
+    act = {"servo": torch.from_numpy(servo).cuda(),
+           "generator_control": {"target_voltage": 80.0, "current_mode": torch.from_numpy(modes).cuda(), "ON_time": 3.0, "OFF_time": 40.0}}
+    done_seen = 0
+    alive = [True] * E                          # a terminated env is frozen here; the oracle must not be stepped on
+    for k in range(STEPS):
+        env.step(act, draws=tape_dev[:, k * SI:(k + 1) * SI].contiguous())
+        f_ref, i_ref = [], []
+        for e, orc in enumerate(oracles):
+            if alive[e]:
+                res = orc.run(SI, [[float(servo[e]), 80.0, int(modes[e]), 3.0, 40.0]], draws=tape[e, k * SI:(k + 1) * SI],
+                              rec_every=0)
+                alive[e] = res["n_done"] == SI
+            f, i = orc.record()
+            i = i.astype(np.int64)
+            i[-1] = int(i[11] or i[12])
+            f_ref.append(f)
+            i_ref.append(i)
+        f_gpu, i_gpu = PU.read_rows(env.engine, range(E))
+        for e in range(E):
+            PU.assert_rows_match(f_gpu[e], i_gpu[e], f_ref[e], i_ref[e], where=f"per-env params env {e} step {k}")
+        done_seen = int(np.stack(i_ref)[:, -1].sum())
+    T = env.wire_temperature.cpu().numpy()
+    for e, orc in enumerate(oracles):
+        err = np.abs(T[e].astype(np.float64) - orc.temperature.astype(np.float64))
+        assert np.all(err <= PU.T_ATOL + PU.T_RTOL * np.abs(orc.temperature)), (e, err.max())
+    assert float(env.state_tensor("stat_sparks").sum()) > 0 and done_seen > 0
+    # a configuration that changes the geometry is refused
+    with pytest.raises(ValueError, match="differs from the batch"):
+        env.set_env_params([0], config=EnvironmentConfig(**dict(CS.README_CFG, workpiece_height=20.0)))

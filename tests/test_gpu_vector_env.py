@@ -23,14 +23,17 @@ def _tape(n_envs, n_us, key):
 THICK = dict(workpiece_height=50.0, wire_diameter=0.25, wire_material="brass", target_cutting_distance=800.0)
 
 
+@pytest.mark.parametrize("in_kernel", [False, True])
 @pytest.mark.parametrize("mode,cfg,seg_len,steps", [("position", README, 0.2, 40), ("velocity", README, 0.2, 12),
                                                     ("position", THICK, 0.1, 10)])
-def test_gap_controller_closed_loop_matches_oracle(mode, cfg, seg_len, steps):
+def test_gap_controller_closed_loop_matches_oracle(mode, cfg, seg_len, steps, in_kernel):
     """BASELINE cfg 3: the batched GapController closes the loop on the device; the oracle is driven
     by the reference's controller arithmetic (run_simulation.py:27-39) evaluated in numpy from its
     own state each control step.  Same injected draws => same trajectories, discrete fields exact.
     The moving servo leaves the dielectric hysteresis band every ~32 µs (in-place refresh path), the
-    40-step run also leaves the debris-density band; the thick case runs two warps per env."""
+    40-step run also leaves the debris-density band; the thick case runs two warps per env.
+    in_kernel: the controller object itself is passed to step(): the same law is evaluated inside the
+    pre-pass and step kernels (SparcController), no torch op between control steps."""
     import torch
     from sparc_b200 import BatchedWireEDMEnv, EnvironmentConfig, GapController
 
@@ -52,7 +55,7 @@ def test_gap_controller_closed_loop_matches_oracle(mode, cfg, seg_len, steps):
     oracles = [O.OracleEnv(**CS.oracle_overrides(case)) for _ in range(E)]
     tape_dev = torch.from_numpy(tape).cuda()
     for k in range(STEPS):
-        env.step(ctrl(env), draws=tape_dev[:, k * SI:(k + 1) * SI].contiguous())
+        env.step(ctrl if in_kernel else ctrl(env), draws=tape_dev[:, k * SI:(k + 1) * SI].contiguous())
         f_ref, i_ref = [], []
         for e, orc in enumerate(oracles):
             f, _ = orc.record()
