@@ -405,7 +405,14 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3((unsigned)blocks);
             cfg.blockDim = dim3((unsigned)threads);
-            cfg.dynamicSmemBytes = 0;
+            // LOG kernels stage rows in dynamic shared memory: two buffers of (N rounded up to 4) floats per env
+            size_t dyn = 0;
+            if (tlog) {
+                const size_t n_stage = ((size_t)p->n_segments + 3) & ~(size_t)3;
+                dyn = 2 * n_stage * sizeof(float) * (v->W == 1 ? SPARC_BLOCK_THREADS / 32 : 1);
+                if (dyn > 40 * 1024) CUDA_TRY(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+            }
+            cfg.dynamicSmemBytes = dyn;
             cfg.stream = (cudaStream_t)stream;
             cudaLaunchAttribute attr[1];
             attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

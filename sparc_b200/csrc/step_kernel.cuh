@@ -290,7 +290,7 @@ static __device__ __noinline__ void mech_self_serve(const SparcParams &P, const 
 template <int K, bool INJECT, int W, bool LOG, bool ALIGNED, int WARPS>
 __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStatePtrs &S, const StepArgs &a, const int e,
                                          float (&sm_halo)[2][W][2], double (&sm_red)[W], WarpRec (&sm_rec)[WARPS],
-                                         float (&sm_log)[LOG ? WARPS : 1][LOG ? 32 * K + 8 : 1])
+                                         float *sm_stage)
 {
     constexpr unsigned FULL = 0xffffffffu;
     static_assert(K % 2 == 0 && K >= 4, "packed stencil: even number of cells per lane, at least two per half");
@@ -468,23 +468,43 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     const int log_rows = logging ? a.total_us / a.log_every : 0;
     int log_ctr = logging ? a.log_every - a.it_base % a.log_every : 0;  // µs until the next sample
     int log_row = logging ? a.it_base / a.log_every : 0;                // next row to write
+    // Row staging for the log (LOG kernels only; dynamic shared memory): two buffers of n_stage floats per env,
+    // the whole row in cell order.  When the rows are 16-byte aligned in the log (N % 4 == 0) a row leaves as ONE
+    // bulk asynchronous copy shared -> global (cp.async.bulk, SASS UBLKCP) issued by one thread, double buffered
+    // so that the next µs's stencil does not wait for it; otherwise as coalesced 4-byte stores.
+    const int n_stage = (N + 3) & ~3;
+    float *stage0 = sm_stage + (size_t)((W == 1) ? wib : 0) * 2 * n_stage;
+    const bool bulk_rows = (N % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.tlog) & 15u) == 0);
+    int log_buf = 0;
+    auto group_sync = [&]() { if constexpr (W > 1) __syncthreads(); else __syncwarp(); };
     auto write_log_row = [&](int r) {
         float *row = a.tlog + ((size_t)e * log_rows + r) * N;
-        float *stage = sm_log[wib];             // this warp's cells in cell order, first cell at stage[0]
-        const int wfirst = __shfl_sync(FULL, geom.cx0, 0);      // first cell of this warp (lane 0's x half is never empty)
+        float *stage = stage0 + log_buf * n_stage;
+        if (bulk_rows) {
+            // the bulk copy issued two rows ago has finished READING this buffer
+            if (gl == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            group_sync();
+        }
 #pragma unroll
         for (int j = 0; j < H; j++) {
-            if (j < geom.nx) stage[geom.cx0 - wfirst + j] = T[j].x;
-            if (j < geom.ny) stage[geom.cy0 - wfirst + j] = T[j].y;
+            if (j < geom.nx) stage[geom.cx0 + j] = T[j].x;
+            if (j < geom.ny) stage[geom.cy0 + j] = T[j].y;
         }
-        __syncwarp();
-        const int last_c = geom.ny ? geom.cy0 + geom.ny : geom.cx0 + geom.nx;   // one past this lane's last cell (0 if none)
-        int wend = last_c;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) wend = max(wend, __shfl_xor_sync(FULL, wend, o));
-        for (int c = wfirst + lane; c < wend; c += 32) row[c] = stage[c - wfirst];
-        __syncwarp();
-        if (gl == 0) row[0] = spoolf;
+        if (gl == 0) stage[0] = spoolf;
+        if (bulk_rows) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> async proxy
+            group_sync();
+            if (gl == 0) {
+                const uint32_t src = (uint32_t)__cvta_generic_to_shared(stage);
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n\tcp.async.bulk.commit_group;"
+                             :: "l"(row), "r"(src), "r"((uint32_t)(N * 4)) : "memory");
+            }
+            log_buf ^= 1;
+        } else {
+            group_sync();
+            for (int c = ((W == 1) ? lane : (int)threadIdx.x); c < N; c += 32 * W) row[c] = stage[c];
+            group_sync();
+        }
     };
     auto log_tick = [&]() {                     // called after every thermal update of a logged env
         if (--log_ctr == 0) {
@@ -844,6 +864,10 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     if (LOG && logging && s.done) {             // rows sampled at or after termination: the frozen field
         for (int r = log_row; r < log_rows; r++) write_log_row(r);
     }
+    if (LOG && logging && bulk_rows) {          // the staging buffers are reused by the next env of this warp / block
+        if (gl == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        group_sync();
+    }
 
 #ifdef SPARC_DBG_TIMES   /* experiments: when and where each env ran, in the unused tail of its trajectory scratch */
     if (gl == 0 && a.n_us <= 1000) {
@@ -944,7 +968,11 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
 // hardware's own refill of freed slots balances equal-length envs just as well, and a capped grid delays the
 // blocks that wait for the registers of the pre-pass kernel.)
 template <int K, bool INJECT, int W, bool LOG, bool ALIGNED>
-__global__ void __launch_bounds__(W == 1 ? SPARC_BLOCK_THREADS : 32 * W, W == 1 ? min_blocks_for(K, ALIGNED) : 1)
+#ifndef SPARC_WARPS_MULTI
+#define SPARC_WARPS_MULTI 16    /* resident warps per SM the block-per-env variants (W > 1) are sized for */
+#endif
+__global__ void __launch_bounds__(W == 1 ? SPARC_BLOCK_THREADS : 32 * W,
+                                  W == 1 ? min_blocks_for(K, ALIGNED) : (SPARC_WARPS_MULTI / W > 0 ? SPARC_WARPS_MULTI / W : 1))
 step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
             const __grid_constant__ StepArgs a)
 {
@@ -953,16 +981,16 @@ step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ Sparc
     __shared__ float sm_halo[2][W][2];
     __shared__ double sm_red[W];
     __shared__ WarpRec sm_rec[WARPS];
-    __shared__ float sm_log[LOG ? WARPS : 1][LOG ? 32 * K + 8 : 1];   // field-log staging, in cell order
+    extern __shared__ __align__(16) float sm_stage[];   // LOG: row staging, 2 buffers per env (host sizes it)
     if constexpr (W == 1) {
         const int stride = (int)gridDim.x * WARPS;
         for (int e = (int)blockIdx.x * WARPS + (int)(threadIdx.x >> 5); e < a.n_envs; e += stride) {
-            step_env<K, INJECT, W, LOG, ALIGNED, WARPS>(P, S, a, e, sm_halo, sm_red, sm_rec, sm_log);
+            step_env<K, INJECT, W, LOG, ALIGNED, WARPS>(P, S, a, e, sm_halo, sm_red, sm_rec, sm_stage);
             __syncwarp();
         }
     } else {
         for (int e = (int)blockIdx.x; e < a.n_envs; e += (int)gridDim.x) {
-            step_env<K, INJECT, W, LOG, ALIGNED, WARPS>(P, S, a, e, sm_halo, sm_red, sm_rec, sm_log);
+            step_env<K, INJECT, W, LOG, ALIGNED, WARPS>(P, S, a, e, sm_halo, sm_red, sm_rec, sm_stage);
             __syncthreads();
         }
     }
