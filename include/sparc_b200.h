@@ -250,6 +250,22 @@ int sparc_step_host(void *state, const SparcParams *p, const SparcActions *actio
                     int n_us, uint64_t seed, uint32_t env_id_base, void *scratch_dev,
                     float *obs_host, void *stream);
 
+/* Allocation-free variant of sparc_step_host.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments and results as sparc_step_host without `scratch_dev`: the action
+ * staging arrays and the observation summary live in a file-scope `static __device__` array inside the library
+ * (1 114 112 bytes, held by every GPU that loads the library until exit), so the call — and everything it calls —
+ * uses no cudaMalloc / cudaFree / allocating routine.  Limit: n_envs <= SPARC_STATIC_MAX_ENVS, more returns
+ * SPARC_E_UNSUPPORTED with a message naming the limit.  The array is shared by EVERY call on a device and keeps
+ * the last call's contents (nothing in it has to start at zero: each call overwrites what it reads); two calls
+ * that overlap on the GPU (different streams or threads) race on it — serialise them, or use sparc_step_host.
+ * Unlike sparc_step_host it always stages through the device array (no in-place path for <= 32 envs), so the
+ * host arrays may be pageable. */
+#define SPARC_STATIC_MAX_ENVS 16384
+int sparc_static_max_envs(void);
+int sparc_step_host_static(void *state, const SparcParams *p, const SparcActions *actions_host, int n_envs,
+                           int n_us, uint64_t seed, uint32_t env_id_base, float *obs_host, void *stream);
+
 /* Measured FP32 FMA issue peak of the current device [TFLOP/s] (dense FFMA micro-kernel, a few
  * ms; synchronous).  Roofline denominator for the compute-bound step kernel; scratch_dev needs
  * >= 4 MiB of device memory. */

@@ -434,6 +434,38 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     return SPARC_OK;
 }
 
+// ---- allocation-free variant of the host-buffer step (sparc_step_host_static) ---------------------
+// The action staging arrays and the observation summary that sparc_step_host keeps in caller-owned device
+// scratch live here instead: a file-scope array every GPU that loads the library holds until exit.
+// Size: the scratch of SPARC_STATIC_MAX_ENVS envs (5 action arrays + SPARC_N_OBS observation rows, each padded
+// to 256 bytes) = 1 114 112 bytes.  Shared by ALL calls on a device: calls that overlap on the GPU race.
+constexpr size_t static_scratch_bytes(size_t n_envs)
+{
+    return ((n_envs * 4 + kAlign - 1) / kAlign * kAlign) * 5 + (n_envs * 4 * SPARC_N_OBS + kAlign - 1) / kAlign * kAlign;
+}
+static __device__ __align__(256) unsigned char g_static_scratch[static_scratch_bytes(SPARC_STATIC_MAX_ENVS)];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is
+// looked up once per device, with that device current, and the kernels are given that pointer.
+int static_scratch_ptr(void **out)
+{
+    constexpr int kMaxDev = 64;
+    static void *ptrs[kMaxDev] = {};
+    static std::atomic<bool> have[kMaxDev];
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDev) return fail(SPARC_E_UNSUPPORTED, "device ordinal beyond 63");
+    if (!have[dev].load(std::memory_order_acquire)) {
+        void *ptr = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void **)&ptr, g_static_scratch));
+        if (!ptr) return fail(SPARC_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        ptrs[dev] = ptr;                          // every thread resolves the same address: a benign double write
+        have[dev].store(true, std::memory_order_release);
+    }
+    *out = ptrs[dev];
+    return SPARC_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -627,6 +659,52 @@ int sparc_step_host(void *state, const SparcParams *p, const SparcActions *ah, i
         CUDA_TRY(cudaMemcpyAsync((void *)ad.off_time, ah->off_time, bytes, cudaMemcpyHostToDevice, st));
     }
     // the observation is written by the step kernel's epilogue (same values as sparc_observe)
+    rc = launch_step(state, p, &ad, n_envs, n_us, seed, env_id_base, nullptr, stream, nullptr, 0, 0, nullptr, 0, obs_dev);
+    if (rc) return rc;
+    if (n_us == 0) {
+        rc = sparc_observe(state, n_envs, p->n_segments, obs_dev, stream);
+        if (rc) return rc;
+    }
+    CUDA_TRY(cudaMemcpyAsync(obs_host, obs_dev, bytes * SPARC_N_OBS, cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return SPARC_OK;
+}
+
+int sparc_static_max_envs(void) { return SPARC_STATIC_MAX_ENVS; }
+
+int sparc_step_host_static(void *state, const SparcParams *p, const SparcActions *ah, int n_envs, int n_us,
+                           uint64_t seed, uint32_t env_id_base, float *obs_host, void *stream)
+{
+    int rc = check_common(state, p, n_envs);
+    if (rc) return rc;
+    if (!ah || !obs_host) return fail(SPARC_E_INVALID, "null host action / obs pointer");
+    if (!ah->servo || !ah->target_voltage || !ah->current_mode || !ah->on_time || !ah->off_time)
+        return fail(SPARC_E_INVALID, "null action array");
+    if (n_envs > SPARC_STATIC_MAX_ENVS) {
+        snprintf(g_err, sizeof(g_err), "sparc_step_host_static: n_envs %d exceeds the static scratch (at most %d envs); "
+                 "use sparc_step_host with caller-owned scratch", n_envs, SPARC_STATIC_MAX_ENVS);
+        return SPARC_E_UNSUPPORTED;
+    }
+    void *scratch = nullptr;
+    rc = static_scratch_ptr(&scratch);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t n = sparc_align_up((size_t)n_envs * 4, kAlign), bytes = (size_t)n_envs * 4;
+    char *d = (char *)scratch;
+    SparcActions ad;
+    ad.servo = (const float *)(d + 0 * n);
+    ad.target_voltage = (const float *)(d + 1 * n);
+    ad.current_mode = (const int32_t *)(d + 2 * n);
+    ad.on_time = (const float *)(d + 3 * n);
+    ad.off_time = (const float *)(d + 4 * n);
+    float *obs_dev = (float *)(d + 5 * n);
+    // nothing in the scratch has to start at zero: the five action arrays are overwritten here and the
+    // kernel writes all SPARC_N_OBS rows of every env (terminated ones included) before they are read back
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.servo, ah->servo, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.target_voltage, ah->target_voltage, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.current_mode, ah->current_mode, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.on_time, ah->on_time, bytes, cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaMemcpyAsync((void *)ad.off_time, ah->off_time, bytes, cudaMemcpyHostToDevice, st));
     rc = launch_step(state, p, &ad, n_envs, n_us, seed, env_id_base, nullptr, stream, nullptr, 0, 0, nullptr, 0, obs_dev);
     if (rc) return rc;
     if (n_us == 0) {
