@@ -484,7 +484,7 @@ def run_gpu_arm(args):
         traffic, inst_per_env_us = None, None
         try:    # dram bytes and executed warp-instructions of one `ncu --set full` capture of this launch
             tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-            key = f"{args.config}:{E}"
+            key = f"{args.config}:{E}" + (f":{n_seg}:{log_every}" if log_every else "")
             if key in tr:
                 traffic = tr[key]["dram_bytes_read"] + tr[key]["dram_bytes_write"]
                 inst_per_env_us = tr[key].get("warp_inst_per_env_us")

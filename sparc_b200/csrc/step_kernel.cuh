@@ -5,13 +5,14 @@
 // by a lane-parallel LOOK-AHEAD exactly as in round 1 (mechanics from the pre-pass kernel, quiet-run
 // detection by ballot, scalar-free stencil runs, exact general µs for everything else).  What is new:
 //
-//   * REGISTER BUDGET.  Everything that is not the field lives in ONE shared-memory record per warp
-//     (WarpRec: the EnvState the general µs works on, the launch bookkeeping, the 32 wire positions
-//     of the current look-ahead block, a window of Philox words).  Across the stencil loops a lane
-//     holds the field (K floats), FOUR convection coefficients, two conduction scalars and a loop
-//     count — the round-1 kernel held 36 coefficient registers and ~40 scalars and sat at 128
-//     registers with spills; this one fits the 72 that 28 resident warps per SM allow, which is what
-//     4096 envs need to run as ONE wave (6.9 warps per scheduler) instead of two.
+//   * SCALAR STATE IN SHARED MEMORY.  Everything that is not the field lives in ONE shared-memory record per
+//     warp (WarpRec: the EnvState the general µs works on, the per-env parameters, the launch bookkeeping, the
+//     32 wire positions of the current look-ahead block, a window of Philox words).  Across the stencil loops a
+//     lane holds the field (K floats), FOUR convection coefficients, two conduction scalars and a loop count —
+//     the round-1 kernel held 36 coefficient registers and ~40 scalars and carried 168 bytes of spills at 128
+//     registers.  The kernel also compiles to 72 registers (28 warps/SM); measured, more resident warps do not
+//     help (the kernel is bound by instruction dispatch, profiles/r02_experiments.txt), so it ships at 128
+//     registers / 16 warps per SM with 16 bytes of spills.
 //   * REGION LAYOUT (SparcLayout, step_common.cuh).  Zone boundaries, the zero-flux end and the pad
 //     slots used to be per-cell coefficient registers (cE, c0, cR per cell).  Now the cells are laid out
 //     so that every such boundary falls between two HALVES of a lane: the conduction coefficient is one
@@ -574,7 +575,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
         // wire positions of this block from the mechanics pre-pass: pos[0] before its first µs,
         // pos[1 + l] after µs l.  They were requested one block AGO (nxt_post: the L2 round trip of
         // ld.global.cg passes under the previous block's stencil runs; it was the largest single stall
-        // of the scalar phase, profiles/r02_v4_ncu_summary.txt); only the first block of a launch waits.
+        // of the scalar phase, profiles/r02_experiments.txt); only the first block of a launch waits.
         {
             int upto = it + nb + 32;
             if (upto > a.n_us) upto = a.n_us;
