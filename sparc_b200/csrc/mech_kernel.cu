@@ -18,7 +18,7 @@ namespace sparc {
 template <int MODE>
 __device__ __forceinline__ bool mech_block_fast(const SparcParams &P, const EnvPrm &q, double &wire, double &v, double &pa, const int it0,
                                                 const int nb, const int first_latch, const double d_old,
-                                                const double d_new, double *traj)
+                                                const double d_new, double *traj, double *trajv)
 {
     const double dt = P.mech_dt, c1 = q.damping_coeff, c2 = q.stiffness_coeff, nw = -q.omega_n;
     const double amax = q.max_acceleration, jmax = q.max_jerk_dt, vmax = q.max_speed;
@@ -40,6 +40,7 @@ __device__ __forceinline__ bool mech_block_fast(const SparcParams &P, const EnvP
         bad = bad || !(fabs(v) <= vmax);
         wire += v * dt;
         traj[it0 + k] = wire;
+        if (trajv) trajv[it0 + k] = v;      // only while signals are sampled
     }
     return !bad;
 }
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
     int first_latch = P.servo_interval - S.t_servo[e];
     if (first_latch < 0) first_latch = 0;
     double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
+    double *trajv = a.signals ? S.mech_trajv + (size_t)e * SPARC_MECH_EPOCH : nullptr;
     double *ck = S.mech_ckpt + (size_t)e * SPARC_MECH_NCKPT * 2;
     uint32_t *prog = (uint32_t *)S.mech_prog + e;
     ck[0] = v;                                  // checkpoint c = state before µs c*SPARC_MECH_CKPT
@@ -74,14 +76,15 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
         const int nb = (a.n_us - it0 < SPARC_MECH_CKPT) ? a.n_us - it0 : SPARC_MECH_CKPT;
         const double w0 = wire, v0 = v, p0 = pa;
         const bool ok = (P.control_mode == 0)
-                            ? mech_block_fast<0>(P, q, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj)
-                            : mech_block_fast<1>(P, q, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj);
+                            ? mech_block_fast<0>(P, q, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj, trajv)
+                            : mech_block_fast<1>(P, q, wire, v, pa, it0, nb, first_latch, d_old, d_new, traj, trajv);
         if (!ok) {                              // a clip was active somewhere in the block: exact path
             wire = w0; v = v0; pa = p0;
 #pragma unroll 1
             for (int k = 0; k < nb; k++) {
                 mech_step(P, q, wire, v, pa, (it0 + k >= first_latch) ? d_new : d_old);
                 traj[it0 + k] = wire;
+                if (trajv) trajv[it0 + k] = v;
             }
         }
         const int b = it0 / SPARC_MECH_CKPT + 1;        // blocks finished

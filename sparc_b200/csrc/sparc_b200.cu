@@ -54,11 +54,12 @@ const FieldDesc kFields[] = {
     {"episode", 'i', sizeof(int32_t)},
     {"T", 'f', sizeof(float)},
     {"mech_traj", 'd', sizeof(double)},
+    {"mech_trajv", 'd', sizeof(double)},
     {"mech_ckpt", 'd', sizeof(double)},
     {"mech_prog", 'i', sizeof(int32_t)},
 };
 constexpr int kNumFields = (int)(sizeof(kFields) / sizeof(kFields[0]));
-constexpr int kFieldT = kNumFields - 4, kFieldTraj = kNumFields - 3, kFieldCkpt = kNumFields - 2;
+constexpr int kFieldT = kNumFields - 5, kFieldTraj = kNumFields - 4, kFieldTrajV = kNumFields - 3, kFieldCkpt = kNumFields - 2;
 
 constexpr size_t kAlign = 256;
 constexpr int SPARC_SELF_MECH_US = 8;
@@ -69,7 +70,7 @@ int padded_segments(int n_segments) { return (int)sparc_align_up((size_t)n_segme
 size_t field_count(int i, int n_envs, int n_segments)
 {
     if (i == kFieldT) return (size_t)n_envs * padded_segments(n_segments);
-    if (i == kFieldTraj) return (size_t)n_envs * SPARC_MECH_EPOCH;
+    if (i == kFieldTraj || i == kFieldTrajV) return (size_t)n_envs * SPARC_MECH_EPOCH;
     if (i == kFieldCkpt) return (size_t)n_envs * SPARC_MECH_NCKPT * 2;
     return (size_t)n_envs;
 }
@@ -96,6 +97,7 @@ SparcStatePtrs make_ptrs(void *state, int n_envs, int n_segments)
     S.episode = (int32_t *)(base + field_offset(idx++, n_envs, n_segments));
     S.T = (float *)(base + field_offset(idx++, n_envs, n_segments));
     S.mech_traj = (double *)(base + field_offset(idx++, n_envs, n_segments));
+    S.mech_trajv = (double *)(base + field_offset(idx++, n_envs, n_segments));
     S.mech_ckpt = (double *)(base + field_offset(idx++, n_envs, n_segments));
     S.mech_prog = (int32_t *)(base + field_offset(idx++, n_envs, n_segments));
     S.n_pad = padded_segments(n_segments);
@@ -158,42 +160,6 @@ __global__ void observe_kernel(SparcStatePtrs S, int n_envs, int n_segments, flo
         obs[9 * (size_t)n_envs + e] = __int_as_float(S.spark_state[e]);
         obs[10 * (size_t)n_envs + e] = __int_as_float(S.t_servo[e]);
         obs[11 * (size_t)n_envs + e] = 0.0f;
-    }
-}
-
-// one warp per env: one row of the per-signal log (SimulationLogger signals, utils/logger.py:105-160,
-// base signal list of experiments/run_simulation.py:126-138) from the stored state, i.e. what
-// `getattr(state, name)` returns after the reference's step() of the same µs.  out: [SPARC_N_SIGNALS][n_envs]
-__global__ void sample_signals_kernel(SparcStatePtrs S, int n_envs, int n_segments, double *out)
-{
-    int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    int lane = threadIdx.x & 31;
-    if (warp >= n_envs) return;
-    const float *row = S.T + (size_t)warp * S.n_pad;
-    float m = -3.0e38f;
-    for (int i = lane; i < n_segments; i += 32) m = fmaxf(m, row[i]);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if (lane == 0) {
-        const int e = warp;
-        const size_t n = (size_t)n_envs;
-        const int fl = S.flags[e];
-        out[SPARC_SIG_TIME * n + e] = (double)S.time[e];
-        out[SPARC_SIG_VOLTAGE * n + e] = S.voltage[e];
-        out[SPARC_SIG_CURRENT * n + e] = S.current[e];
-        out[SPARC_SIG_WIRE_POSITION * n + e] = S.wire[e];
-        out[SPARC_SIG_WIRE_VELOCITY * n + e] = S.v[e];
-        out[SPARC_SIG_WORKPIECE_POSITION * n + e] = S.wp[e];
-        out[SPARC_SIG_TARGET_DELTA * n + e] = S.target_delta[e];
-        out[SPARC_SIG_DEBRIS_DENSITY * n + e] = S.debris_density[e];
-        out[SPARC_SIG_FLOW_RATE * n + e] = S.flow[e];
-        out[SPARC_SIG_IS_SHORT_CIRCUIT * n + e] = (fl & SPARC_F_SHORT) ? 1.0 : 0.0;
-        out[SPARC_SIG_SPARK_STATE * n + e] = (double)S.spark_state[e];
-        out[SPARC_SIG_MAX_TEMPERATURE * n + e] = (double)m;
-        out[SPARC_SIG_AVERAGE_TEMPERATURE * n + e] = S.wire_avg_T[e];
-        out[SPARC_SIG_DEBRIS_VOLUME * n + e] = S.debris_volume[e];
-        out[SPARC_SIG_TIME_IN_CRITICAL * n + e] = (double)S.crit_count[e];
-        out[SPARC_SIG_FLAGS * n + e] = (double)fl;
     }
 }
 
@@ -358,24 +324,19 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     if (n_us == 0) return SPARC_OK;
     if (ctrl && ctrl->kind != 0) {
         if (ctrl->kind != 1) return fail(SPARC_E_INVALID, "unknown controller kind");
-        if (n_us > SPARC_MECH_EPOCH || signals) return fail(SPARC_E_UNSUPPORTED, "in-kernel controller: single-launch calls only (n_us <= 1024, no signal sampling)");
+        if (n_us > SPARC_MECH_EPOCH) return fail(SPARC_E_UNSUPPORTED, "in-kernel controller: single-launch calls only (n_us <= 1024)");
     }
     sparc::SparcLayout lay;
     const Variant *v = pick_variant(p, &lay);
     if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6145 wire segments)");
     SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
-    const sparc::StepFn fn = v->fn[tlog ? 1 : 0][draws ? 1 : 0][lay.aligned ? 1 : 0];
+    const sparc::StepFn fn = v->fn[(tlog || signals) ? 1 : 0][draws ? 1 : 0][lay.aligned ? 1 : 0];
     int blocks, threads;
     launch_geometry(v, n_envs, &blocks, &threads);
-    // one (mechanics pre-pass, fused step) pair per chunk: at most SPARC_MECH_EPOCH µs, cut at every
-    // signal-sampling µs (the signal rows are read from the stored state between launches)
+    // one (mechanics pre-pass, fused step) pair per chunk of at most SPARC_MECH_EPOCH µs
     int t = 0;
     while (t < n_us) {
         int n = (n_us - t < SPARC_MECH_EPOCH) ? n_us - t : SPARC_MECH_EPOCH;
-        if (signals) {
-            const int to_sample = sample_every - t % sample_every;
-            if (n > to_sample) n = to_sample;
-        }
         sparc::StepArgs a;
         a.act = *actions;
         a.n_envs = n_envs;
@@ -387,6 +348,8 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
         a.log_every = log_every;
         a.n_log_envs = n_log_envs;
         a.it_base = t;
+        a.signals = signals;              // rows are written by the step kernel itself (LOG instantiations)
+        a.sample_every = signals ? sample_every : 0;
         a.total_us = n_us;
         a.obs = (t + n >= n_us) ? obs : nullptr;    // the last launch of the call writes the observation
         // The pre-pass and the step kernel OVERLAP: mech_kernel triggers programmatic launch completion
@@ -407,7 +370,7 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
             cfg.blockDim = dim3((unsigned)threads);
             // LOG kernels stage rows in dynamic shared memory: two buffers of (N rounded up to 4) floats per env
             size_t dyn = 0;
-            if (tlog) {
+            if (tlog || signals) {
                 const size_t n_stage = ((size_t)p->n_segments + 3) & ~(size_t)3;
                 dyn = 2 * n_stage * sizeof(float) * (v->W == 1 ? SPARC_BLOCK_THREADS / 32 : 1);
                 if (dyn > 40 * 1024) CUDA_TRY(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
@@ -424,11 +387,6 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
             CUDA_TRY(cudaLaunchKernelEx(&cfg, fn, *p, S, a));
         }
         t += n;
-        if (signals && t % sample_every == 0) {
-            const int sthreads = 128, sblocks = (n_envs * 32 + sthreads - 1) / sthreads;
-            sample_signals_kernel<<<sblocks, sthreads, 0, (cudaStream_t)stream>>>(
-                S, n_envs, p->n_segments, signals + (size_t)(t / sample_every - 1) * SPARC_N_SIGNALS * n_envs);
-        }
     }
     CUDA_TRY(cudaGetLastError());
     return SPARC_OK;

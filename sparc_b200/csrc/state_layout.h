@@ -129,6 +129,7 @@ struct SparcStatePtrs {
     int32_t *episode;
     float *T;       // [n_envs][n_pad]
     double *mech_traj;   // [n_envs][SPARC_MECH_EPOCH]
+    double *mech_trajv;  // [n_envs][SPARC_MECH_EPOCH] wire velocity after each µs — written only while signals are sampled
     double *mech_ckpt;   // [n_envs][SPARC_MECH_NCKPT][2]
     int32_t *mech_prog;  // [n_envs] launch tag + number of SPARC_MECH_CKPT-µs blocks the pre-pass has published
     int32_t n_pad;

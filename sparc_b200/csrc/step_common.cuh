@@ -110,6 +110,8 @@ struct StepArgs {
     int it_base, total_us;   // this launch covers µs [it_base, it_base + n_us) of a call of total_us µs
     float *obs;              // observation summary [SPARC_N_OBS][n_envs] written by the kernel epilogue, or NULL
     uint32_t mech_seq;       // tag of this launch pair in SparcStatePtrs::mech_prog (multiple of 64)
+    double *signals;         // per-signal log [total_us / sample_every][SPARC_N_SIGNALS][n_envs] of this CALL, or NULL
+    int sample_every;
     SparcLayout lay;
     SparcController ctrl;    // kind 0: the servo command is act.servo[e]
 };
@@ -188,6 +190,7 @@ struct EnvState {
     double fin_wire, fin_v, fin_pa;              // mechanics state to store at the end of the launch
     double lam_bound;                            // upper bound of lambda(gap) over all gaps
     double cfac;                                 // f = temp_update_factor
+    double avg_view;                             // EDMState.wire_average_temperature as the reference holds it now
     int crit_count, w_zone_counter, next_latch, skip_flush, tsi_break, time0, first_latch_it;
     int win_short0, win_steps0, win_steps_out;
     uint32_t w_thresh;                           // Philox word >= w_thresh can never ignite
@@ -203,6 +206,7 @@ struct EnvState {
 struct __align__(16) WarpRec {
     uint32_t rng[32][4];
     double pos[33];
+    double vel[33];          // wire velocity after µs l of the block at vel[1 + l] (only while signals are sampled)
     EnvState s;
 };
 
@@ -242,6 +246,25 @@ __device__ __forceinline__ void materialize(EnvState &s, const SparcParams &P)
             s.debris_volume = (nv > 0.0) ? nv : 0.0;
         }
         s.pend_flush = false;
+    }
+}
+
+// What the reference holds in (debris_density, debris_volume) after the last executed µs, WITHOUT touching the
+// lazily kept state (signal rows sampled in the middle of a launch).  Same arithmetic as materialize().
+__device__ __forceinline__ void dielectric_view(const EnvState &s, const SparcParams &P, double &dens, double &vol)
+{
+    const bool dens_valid = s.dens_valid && !s.ran_fast, pend = s.pend_flush || s.ran_fast;
+    dens = s.debris_density;
+    if (!dens_valid) {
+        const double g = (s.gap_prev > 0.001) ? s.gap_prev : 0.001;
+        const double cavity = P.cavity_volume_coeff * (g * 0.001);
+        if (cavity > 0.0) { const double d = s.debris_volume / cavity; dens = (d < 1.0) ? d : 1.0; }
+        else dens = 0.0;
+    }
+    vol = s.debris_volume;
+    if (pend && s.flow > 0.001 && vol > 0.001) {
+        const double nv = vol - s.q.debris_removal_per_us * s.flow;
+        vol = (nv > 0.0) ? nv : 0.0;
     }
 }
 

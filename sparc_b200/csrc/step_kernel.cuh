@@ -271,6 +271,7 @@ static __device__ __noinline__ void mech_self_serve(const SparcParams &P, const 
 {
     const int e = s.e;
     double *traj = S.mech_traj + (size_t)e * SPARC_MECH_EPOCH;
+    double *trajv = a.signals ? S.mech_trajv + (size_t)e * SPARC_MECH_EPOCH : nullptr;
     double *ck = S.mech_ckpt + (size_t)e * SPARC_MECH_NCKPT * 2;
     double wire = s.wire0, v = S.v[e], pa = S.prev_accel[e];
     ck[0] = v; ck[1] = pa;
@@ -278,6 +279,7 @@ static __device__ __noinline__ void mech_self_serve(const SparcParams &P, const 
     for (int k = 0; k < upto; k++) {
         mech_step(P, s.q, wire, v, pa, (k >= s.first_latch_it) ? s.delta_new0 : s.delta_old0);
         traj[k] = wire;
+        if (trajv) trajv[k] = v;
         if ((k + 1) % SPARC_MECH_CKPT == 0) { ck[2 * ((k + 1) / SPARC_MECH_CKPT)] = v; ck[2 * ((k + 1) / SPARC_MECH_CKPT) + 1] = pa; }
         if (k + 1 == a.n_us) { ck[2 * (SPARC_MECH_NCKPT - 1)] = v; ck[2 * (SPARC_MECH_NCKPT - 1) + 1] = pa; }
     }
@@ -342,6 +344,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     s.time = S.time[e]; s.spark_state = S.spark_state[e]; s.spark_dur = S.spark_dur[e]; s.flags = S.flags[e];
     s.crit_count = S.crit_count[e];
     s.w_zone_counter = S.w_zone_counter[e];
+    s.avg_view = P.compute_zone_mean ? S.w_last_zone_mean[e] : S.wire_avg_T[e];
     s.time0 = s.time;
     s.latch_time = s.time - S.t_servo[e];
     s.tse_ref = s.time - S.t_spark_end[e];
@@ -362,7 +365,8 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
 
     if (s.flags & SPARC_F_DONE) {               // terminated envs are left untouched
         if (s.writer && !cont) { S.win_vsum[e] = 0.0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0; }
-        if (a.obs) {                            // observation of a frozen env, from the stored state
+        const bool frozen_rows = LOG && a.signals != nullptr && a.sample_every > 0 && a.it_base == 0;
+        if (a.obs || frozen_rows) {             // observation / signal rows of a frozen env, from the stored state
             float m = -3.0e38f;
             for (int c = gl; c < N; c += 32 * W) m = fmaxf(m, Trow[c]);
 #pragma unroll
@@ -372,7 +376,16 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                 __syncthreads();
                 for (int w = 0; w < W; w++) m = fmaxf(m, (float)sm_red[w]);
             }
-            if (s.writer) {
+            if (s.writer && frozen_rows) {      // every sample of this call sees the frozen state (the reference's
+                const size_t ne = (size_t)a.n_envs;                    // logger would read the same EDMState again)
+                const double vals[SPARC_N_SIGNALS] = {
+                    (double)s.time, s.voltage, S.current[e], s.wire, s.v, s.wp, s.target_delta, s.debris_density, s.flow,
+                    (s.flags & SPARC_F_SHORT) ? 1.0 : 0.0, (double)s.spark_state, (double)m, S.wire_avg_T[e], s.debris_volume,
+                    (double)s.crit_count, (double)s.flags};
+                for (int r = 0; r < a.total_us / a.sample_every; r++)
+                    for (int k = 0; k < SPARC_N_SIGNALS; k++) a.signals[((size_t)r * SPARC_N_SIGNALS + k) * ne + e] = vals[k];
+            }
+            if (s.writer && a.obs) {
                 const size_t ne = (size_t)a.n_envs;
                 const int steps = cont ? s.win_steps0 : 0;
                 a.obs[0 * ne + e] = (float)(s.wp - s.wire);
@@ -515,6 +528,58 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
         }
     };
 
+    // per-signal log (SimulationLogger scalar signals, utils/logger.py:105-160): row r of the CALL holds what the
+    // reference's `getattr(state, name)` returns after µs (r+1)*sample_every - 1.  Written by this kernel: quiet runs
+    // are cut at the sampling µs, the lazily kept dielectric state is read through dielectric_view().
+    const bool sig_on = LOG && a.signals != nullptr && a.sample_every > 0;
+    const int sig_rows = sig_on ? a.total_us / a.sample_every : 0;
+    int sig_ctr = sig_on ? a.sample_every - a.it_base % a.sample_every : 0;  // µs until the next sample
+    int sig_row = sig_on ? a.it_base / a.sample_every : 0;
+    auto env_max_T = [&]() {                    // max over the env's cells; every thread of the env calls it
+        float m = lane_max<H>(T, lf, spoolf);   // cell 0 is spoolf
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
+        if constexpr (W > 1) {
+            __syncthreads();
+            if (lane == 0) sm_red[ctx.wid] = (double)m;
+            __syncthreads();
+            for (int w = 0; w < W; w++) m = fmaxf(m, (float)sm_red[w]);
+        }
+        return m;
+    };
+    auto sig_write = [&](int r, double time_v, double voltage, double current, double wire, double v, double dens, double vol,
+                         int flags, int spark_state, float tmax, double avg_T, int crit) {
+        if (gl != 0 || r >= sig_rows) return;
+        const size_t ne = (size_t)a.n_envs;
+        double *row = a.signals + (size_t)r * SPARC_N_SIGNALS * ne + e;
+        row[SPARC_SIG_TIME * ne] = time_v;
+        row[SPARC_SIG_VOLTAGE * ne] = voltage;
+        row[SPARC_SIG_CURRENT * ne] = current;
+        row[SPARC_SIG_WIRE_POSITION * ne] = wire;
+        row[SPARC_SIG_WIRE_VELOCITY * ne] = v;
+        row[SPARC_SIG_WORKPIECE_POSITION * ne] = s.wp;
+        row[SPARC_SIG_TARGET_DELTA * ne] = s.target_delta;
+        row[SPARC_SIG_DEBRIS_DENSITY * ne] = dens;
+        row[SPARC_SIG_FLOW_RATE * ne] = s.flow;
+        row[SPARC_SIG_IS_SHORT_CIRCUIT * ne] = (flags & SPARC_F_SHORT) ? 1.0 : 0.0;
+        row[SPARC_SIG_SPARK_STATE * ne] = (double)spark_state;
+        row[SPARC_SIG_MAX_TEMPERATURE * ne] = (double)tmax;
+        row[SPARC_SIG_AVERAGE_TEMPERATURE * ne] = avg_T;
+        row[SPARC_SIG_DEBRIS_VOLUME * ne] = vol;
+        row[SPARC_SIG_TIME_IN_CRITICAL * ne] = (double)crit;
+        row[SPARC_SIG_FLAGS * ne] = (double)flags;
+    };
+    auto sig_emit = [&](double wire, double v) { // the state after the µs just executed (not terminated)
+        const float m = env_max_T();
+        double dens, vol;
+        dielectric_view(s, P, dens, vol);
+        const int st = s.spark_state;
+        sig_write(sig_row, (double)s.time, s.voltage, (st == 1 || st == -1) ? s.ipk : 0.0, wire, v, dens, vol, s.flags, st, m,
+                  s.avg_view, s.crit_count);
+        sig_row += 1;
+        sig_ctr = a.sample_every;
+    };
+
     // mechanics pre-pass results of this launch (mech_kernel).  The pre-pass is STILL RUNNING while this
     // kernel executes (programmatic dependent launch, sparc_b200.cu): positions and checkpoints are
     // read only after the producer thread of this env has published them through mech_prog
@@ -598,6 +663,12 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             if (lane == 0) R.pos[0] = p0;
             prev_nb = nb;
         }
+        if (sig_on) {                           // velocities after each µs of this block (published with the positions)
+            __syncwarp();
+            R.vel[lane + 1] = __ldcg(S.mech_trajv + (size_t)e * SPARC_MECH_EPOCH + it + ((lane < nb) ? lane : nb - 1));
+        }
+        unsigned stop_cache = 0;                // LOG: the look-ahead's stop mask of this block, valid while runs are
+        bool stop_ok = false;                   // only cut at sampling µs (nothing it depends on has changed)
         const int blk_time = s.time;
         // ignition rolls (slot 2): word t&3 of Philox block t>>2; each lane computes one counter of a
         // 32-counter window and keeps all four words: one refill serves 125..128 µs
@@ -618,7 +689,18 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             int n = 0;
             int off_tr = -1;                    // run offset of the rest -> idle transition µs
             const int spark_state = s.spark_state;
-            if (!force_general && s.fast_ok && (spark_state == 0 || spark_state == -2)) {
+            bool from_cache = false;
+            if (LOG && stop_ok && !force_general && !((stop_cache >> i) & 1u)) {
+                // the previous run was cut at a sampling µs, not by a stop: the mask still holds
+                const unsigned stop = stop_cache >> i;
+                n = stop ? __ffs(stop) - 1 : 32 - i;
+                if (spark_state == -2) {
+                    off_tr = s.onoff_thr - s.spark_dur - 1;
+                    if (off_tr < 0) off_tr = 0;
+                }
+                from_cache = true;
+            }
+            if (!from_cache && !force_general && s.fast_ok && (spark_state == 0 || spark_state == -2)) {
                 const double pre_l = R.pos[lane], post_l = R.pos[lane + 1];
                 const double wp = s.wp, debris_volume = s.debris_volume;
                 const double g = wp - pre_l;
@@ -660,7 +742,9 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                         ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
                     }
                 }
-                unsigned stop = __ballot_sync(FULL, !(ok && in_band())) >> i;
+                unsigned stop = __ballot_sync(FULL, !(ok && in_band()));
+                if (LOG) { stop_cache = stop; stop_ok = true; }
+                stop >>= i;
                 n = stop ? __ffs(stop) - 1 : 32 - i;
                 if (n == 0 && ((__ballot_sync(FULL, ok) >> i) & 1u)) {
                     // only a band failed on µs i: refresh the hysteresis state in place (light_refresh)
@@ -674,13 +758,16 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                             double deb_lo = dv2;
                             if (dv2 > 0.001) deb_lo = dv2 - (double)(off + 1) * s.flush_amt - 1e-14;
                             b = b && deb_lo >= s.lo_c * g && dv2 <= s.hi_c * g;
-                            stop = __ballot_sync(FULL, !(ok && b)) >> i;
+                            stop = __ballot_sync(FULL, !(ok && b));
+                            if (LOG) { stop_cache = stop; stop_ok = true; }
+                            stop >>= i;
                             n = stop ? __ffs(stop) - 1 : 32 - i;
                         }
                     }
                 }
             }
             force_general = false;
+            if (LOG && sig_on && n > sig_ctr) n = sig_ctr;      // a sampling µs is always the last µs of a run
 
             if (n > 0) {
                 // ================= quiet run ===================================================
@@ -738,10 +825,15 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                 }
                 s.time += nx;
                 i += nx;
+                if (LOG && sig_on) {
+                    sig_ctr -= nx;
+                    if (sig_ctr == 0) sig_emit(R.pos[i], R.vel[i]);
+                }
                 continue;
             }
 
             // ================= general µs ======================================================
+            stop_ok = false;
             s.wire = R.pos[i];
             s.it = it + i;
             if (s.ran_fast) { s.dens_valid = false; s.pend_flush = true; s.ran_fast = false; }
@@ -834,6 +926,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                     }
                     const double zm = (double)(float)(tot / (double)(zb - za));
                     if (s.writer) { S.w_last_zone_mean[e] = zm; S.wire_avg_T[e] = zm; }
+                    s.avg_view = zm;
                     s.zone_mean_written = true;
                     s.w_zone_counter = 0;
                 }
@@ -854,6 +947,10 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             else if (s.wp >= s.q.target_position) { s.flags |= SPARC_F_TARGET; s.done = true; }
             if (s.done) { rewind_mech(it + i + 1); break; }
             i += 1;
+            if (LOG && sig_on) {
+                sig_ctr -= 1;
+                if (sig_ctr == 0) sig_emit(R.pos[i], R.vel[i]);
+            }
         }
         it += nb;
     }
@@ -933,6 +1030,16 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
         S.stat_steps[e] += win_steps;
         S.win_sparks[e] = s.win_sparks; S.win_short_us[e] = s.win_short_us; S.win_steps[e] = s.win_steps0 + win_steps;
         s.win_steps_out = win_steps;
+    }
+    if (LOG && sig_on && s.done) {              // samples at or after the terminating µs: the final state, as stored
+        const float m = env_max_T();
+        if (gl == 0) {
+            const int st = s.spark_state;
+            const double avg = S.wire_avg_T[e];
+            for (int r = sig_row; r < sig_rows; r++)
+                sig_write(r, (double)s.time, s.voltage, (st == 1 || st == -1) ? s.ipk : 0.0, s.fin_wire, s.fin_v, s.debris_density,
+                          s.debris_volume, s.flags, st, m, avg, s.crit_count);
+        }
     }
     // ---------------- observation summary (what sparc_observe computes from the stored state) ----
     if (a.obs) {
