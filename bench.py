@@ -335,16 +335,21 @@ def run_gpu_arm(args):
             ev[k][0].record()
             one_step()
             launches += 2                               # mechanics pre-pass + fused step kernel
-            if world > 1 and (k + 1) % 10 == 0:         # cfg 4: episode stats all-reduce every 10 control steps
+            if world > 1 and (k + 1) % 10 == 0 and not os.environ.get("SPARC_BENCH_NO_ALLREDUCE"):   # cfg 4: episode stats all-reduce every 10 control steps
                 dist.all_reduce(eng.reduce_stats())
                 launches += 1
             ev[k][1].record()
         barrier()
         step_ms = [a.elapsed_time(b) for a, b in ev]
         total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+        per_rank = [float(total_ms.item()) / K]
         if world > 1:
+            allr = [torch.zeros_like(total_ms) for _ in range(world)]
+            dist.all_gather(allr, total_ms)
+            per_rank = [float(t.item()) / K for t in allr]
             dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
         total_s = float(total_ms.item()) * 1e-3
+        device_arm.per_rank_ms = per_rank
         return world * envs * si * K / total_s, step_ms, launches, total_s
 
     eng = make_engine(E)
@@ -352,9 +357,10 @@ def run_gpu_arm(args):
 
     # ---- device-resident arm ------------------------------------------------------------------
     sampler = ClockSampler(local_rank)
-    sampler.start()                                 # samples cover warm-up + timed region (all under load)
+    if rank == 0:                                   # one poller per box: eight of them perturb an 8-GPU run
+        sampler.start()                             # samples cover warm-up + timed region (all under load)
     t_s = time.perf_counter()
-    while len(sampler.lines) < 3 and time.perf_counter() - t_s < 3.0:   # nvidia-smi needs ~0.2 s for its first line:
+    while rank == 0 and len(sampler.lines) < 3 and time.perf_counter() - t_s < 3.0:   # nvidia-smi needs ~0.2 s for its first line:
         eng.step(si)                                # keep the GPU under the same load until it reports,
         if eng["time"][0].item() > 150_000:         # so that even a 10-ms timed region has clock samples
             eng.reset(); eng.set_actions(*action)
@@ -364,7 +370,8 @@ def run_gpu_arm(args):
     t_wall0 = time.perf_counter()
     value, step_ms, launches, total_s = device_arm(eng, E, K, max(args.warmup, 3), tlog)
     t_wall = time.perf_counter() - t_wall0
-    clocks = sampler.stop()
+    clocks = sampler.stop() if rank == 0 else None
+    per_rank_ms = list(device_arm.per_rank_ms)
 
     # ---- end-to-end arm: C-ABI call with host buffers (H2D actions, D2H observation) ----------
     # Same workload as the device arm: cfg3 evaluates the gap controller on the HOST from the returned
@@ -453,7 +460,8 @@ def run_gpu_arm(args):
         envs_s = eng.n_envs
         n_s = max(200, int(2.2 / max(1e-4, sum(step_ms) / len(step_ms) * 1e-3)))
         smp = ClockSampler(local_rank)
-        smp.start()
+        if rank == 0:
+            smp.start()
         for _ in range(5):
             eng.step(si)
         barrier()
@@ -470,7 +478,7 @@ def run_gpu_arm(args):
             dist.all_reduce(sus_ms, op=dist.ReduceOp.MAX)
         sustained = {"value": world * envs_s * si * n_s / (float(sus_ms.item()) * 1e-3), "unit": UNIT, "steps": n_s,
                      "seconds": float(sus_ms.item()) * 1e-3, "envs_per_gpu": envs_s, "l2": "not flushed (back-to-back launches)",
-                     "clocks": smp.stop()}
+                     "clocks": smp.stop() if rank == 0 else None}
 
     if rank == 0:
         fp32_peak = measure_fp32_peak(dev)
@@ -521,6 +529,7 @@ def run_gpu_arm(args):
                     "api": ("sparc_step_host (C-ABI, pinned host action/observation buffers)" if tlog is None else
                             "sparc_step_logged + D2H of the logged field to pinned host memory")},
             "gpu_launches": launches,
+            "per_rank_ms_per_step": per_rank_ms,
             "clocks": clocks,
             "roofline": hbm_roof if hbm_bound else fp32_roof,
             ("roofline_fp32" if hbm_bound else "roofline_hbm"): fp32_roof if hbm_bound else hbm_roof,

@@ -171,6 +171,14 @@ int sparc_init(void *state, const SparcParams *p, int n_envs, void *stream);
  * mask byte is non-zero (mask == NULL: all).  `episode` increments for reset envs. */
 int sparc_reset(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream);
 
+/* The reference's OWN reset semantics (strict_reference_reset): `WireEDMEnv.reset()` re-creates only
+ * EDMState (wire_edm.py:106-114); everything its module objects keep on themselves survives into the next episode —
+ * short-circuit countdowns and the peak-current cache (ignition.py:75-83), prev_accel (mechanics.py:60), debris volume,
+ * flow condition, ion channel and hysteresis memory (dielectric.py:69-80), convection coefficients and the zone-mean
+ * cache (wire.py:204-225).  sparc_reset clears all of it (a freshly constructed env); this entry point clears only what
+ * the reference clears.  Pinned against the running reference: tests/golden/reference_reset.npz. */
+int sparc_reset_reference(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream);
+
 /* sparc_reset with the episode counter of the reset envs set back to 0: the state a freshly
  * initialised blob has.  This is `reset(seed=s)` (wire_edm.py:106-107 re-seeds np_random through
  * gym.Env.reset): the same seed must replay the same episode, so the Philox counter word that

@@ -140,6 +140,7 @@ def lib():
         L.or_create.argtypes = [C.POINTER(OrParams)]
         L.or_destroy.argtypes = [C.c_void_p]
         L.or_reset.argtypes = [C.c_void_p]
+        L.or_reset_reference.argtypes = [C.c_void_p]
         L.or_n_segments.argtypes = [C.c_void_p]
         L.or_geometry.argtypes = [C.c_void_p, C.POINTER(_I)]
         L.or_temperature.restype = C.POINTER(C.c_float)
@@ -188,8 +189,10 @@ class OracleEnv:
             lib().or_destroy(self._h)
             self._h = None
 
-    def reset(self):
-        lib().or_reset(self._h)
+    def reset(self, reference_semantics: bool = False):
+        """Fresh-env reset, or (reference_semantics=True) the reference's own reset(): only EDMState is
+        re-created, module-internal state survives (wire_edm.py:106-114)."""
+        (lib().or_reset_reference if reference_semantics else lib().or_reset)(self._h)
 
     def geometry(self):
         out = (_I * 5)()

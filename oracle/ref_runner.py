@@ -156,8 +156,8 @@ def make_action(servo, target_voltage, current_mode, on_time, off_time):
 def run_reference(env, draws: np.ndarray, n_us: int,
                   controller: Callable[[object, int], dict],
                   per_us: bool = True, t_every: int = 1000,
-                  initial: Optional[dict] = None):
-    """Reset `env`, inject `draws`, run up to `n_us` step() calls (stops at termination).
+                  initial: Optional[dict] = None, do_reset: bool = True):
+    """Reset `env` (unless do_reset=False: the caller did, e.g. a second episode on used modules), inject `draws`, run up to `n_us` step() calls (stops at termination).
 
     controller(env, ctrl_index) -> action dict; called before the first step and after
     every step whose info["control_step"] is True (the loop of README.md:101-106 /
@@ -165,7 +165,8 @@ def run_reference(env, draws: np.ndarray, n_us: int,
       f64[n,len(F64_FIELDS)], i32[n,len(I32_FIELDS)] per µs (or per control step when
       per_us=False), T[k,N] snapshots every `t_every` µs, actions[c,5] that were passed.
     """
-    env.reset(seed=0)
+    if do_reset:
+        env.reset(seed=0)
     if initial:
         for k, v in initial.items():
             setattr(env.state, k, v)

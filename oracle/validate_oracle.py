@@ -109,12 +109,54 @@ def compare(name, ref, orc, verbose=True):
     return ok, worst, (float(dT.max()) if nT else 0.0)
 
 
+RESET_CASE, RESET_N1, RESET_N2 = "debris_shorts", 3200, 4000
+
+
+def run_reference_reset_case():
+    """Second episode on USED modules: run RESET_N1 µs of the debris_shorts case (short-circuit countdowns, debris,
+    hysteresis memory, convection all active), call the reference's reset(), run RESET_N2 µs with a second tape.
+    Returns (case, tape1, tape2, ref1, ref2)."""
+    case = CS.CASES[RESET_CASE]
+    env = RR.make_env(case.get("config"), case.get("mode", "position"), ignition=case.get("ignition"),
+                      wire=case.get("wire"), material=case.get("material"), dielectric=case.get("dielectric"),
+                      mechanics=case.get("mechanics"))
+    tape1 = CS.make_tape(4101, RESET_N1)
+    tape2 = CS.make_tape(4102, RESET_N2)
+    ctl = reference_controller(case)
+    ref1 = RR.run_reference(env, tape1, RESET_N1, ctl, per_us=True, t_every=1000)
+    env.reset()                                   # the reference's reset: new EDMState, modules untouched
+    ref2 = RR.run_reference(env, tape2, RESET_N2, ctl, per_us=True, t_every=1000, do_reset=False)
+    geo = np.array([env.wire.n_segments, env.wire.zone_start, env.wire.zone_end, env.wire.contact_bottom_idx,
+                    env.wire.contact_top_idx])
+    ref1["geometry"] = ref2["geometry"] = geo
+    return case, tape1, tape2, ref1, ref2
+
+
+def check_reference_reset(write_golden=False):
+    case, tape1, tape2, ref1, ref2 = run_reference_reset_case()
+    e = O.OracleEnv(**CS.oracle_overrides(case))
+    o1 = e.run(RESET_N1, ref1["actions"], draws=tape1, rec_every=1, t_every=1000)
+    e.reset(reference_semantics=True)
+    o2 = e.run(RESET_N2, ref2["actions"], draws=tape2, rec_every=1, t_every=1000)
+    o1["geometry"] = o2["geometry"] = np.array(list(e.geometry().values()))
+    ok1, _, _ = compare("reference_reset/episode1", ref1, o1)
+    ok2, _, _ = compare("reference_reset/episode2", ref2, o2)
+    carried = dict(short_us_first_100=int(ref2["i32"][:100, 6].sum()), debris_volume_t0=float(ref2["f64"][0, 6]))
+    print(f"{'OK  ' if ok1 and ok2 else 'FAIL'} reference_reset: episode 2 starts with {carried}")
+    if write_golden:
+        n = len(ref2["f64"])
+        np.savez_compressed(os.path.join(GOLDEN_DIR, "reference_reset.npz"), f64=ref2["f64"], i32=ref2["i32"].astype(np.int32),
+                            T=ref2["T"], T_times=ref2["T_times"], actions1=ref1["actions"], actions2=ref2["actions"],
+                            n1=np.array([RESET_N1]), n2=np.array([n]))
+    return ok1 and ok2
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("cases", nargs="*")
     ap.add_argument("--write-golden", action="store_true")
     args = ap.parse_args()
-    names = args.cases or list(CS.CASES)
+    names = [c for c in args.cases if c != "reference_reset"] or ([] if args.cases else list(CS.CASES))
     all_ok = True
     for name in names:
         case, tape, ref = run_case_reference(name)
@@ -140,6 +182,8 @@ def main():
                 T=ref["T"], T_times=ref["T_times"], actions=ref["actions"],
                 geometry=ref["geometry"], n_done=np.array([ref["n_done"]]), avg_T=ref["avg_T"],
                 consumed=np.packbits(ref["consumed"], axis=0))
+    if not args.cases or "reference_reset" in args.cases:
+        all_ok &= check_reference_reset(args.write_golden)
     print("ALL OK" if all_ok else "SOME FAILED")
     return 0 if all_ok else 1
 

@@ -184,6 +184,34 @@ void or_reset(OrEnv *e)
     e->spark_y = -1.0;
 }
 
+/* The REFERENCE's reset() (wire_edm.py:106-114): a new EDMState() with workpiece_position = initial_gap and
+ * target_position = target_cutting_distance — and nothing else.  Everything the module objects keep on
+ * themselves survives: ignition's short-circuit countdowns and current cache (ignition.py:75-83),
+ * mechanics' prev_accel (mechanics.py:60), the dielectric's debris volume / flow condition / ion channel /
+ * hysteresis memory (dielectric.py:69-80), the wire's convection array, flow memory and zone-mean cache
+ * (wire.py:204-225), material's crater cache (material.py:46-47).  The new state's wire_temperature is empty
+ * and is re-filled with spool_T by the next WireModule.update (wire.py:264-269). */
+void or_reset_reference(OrEnv *e)
+{
+    const OrParams *p = &e->p;
+    e->time = e->t_servo = e->t_open_v = e->t_spark_ign = e->t_spark_end = 0;
+    e->voltage = e->current = 0.0;
+    e->target_voltage = e->on_time = e->off_time = 0.0;
+    e->current_mode = 0;
+    e->wp = p->initial_gap; e->wire = 0.0; e->v = 0.0; e->unwind_v = 0.2;
+    for (int i = 0; i < e->n; i++) e->T[i] = (float)p->spool_T;
+    e->crit_count = 0;
+    e->wire_avg_T = 0.0;
+    e->spark_state = 0; e->spark_dur = 0; e->spark_y = -1.0; e->has_y = 0;
+    /* debris_volume is the DielectricModule's own accumulator here (dielectric.py:69): it survives */
+    e->dielectric_T = 0.0; e->debris_density = 0.0; e->cavity_volume = 0.0;
+    e->flow_rate = 0.0; e->last_crater_volume = 0.0;
+    e->is_short = 0; e->broken = 0; e->target_reached = 0;
+    e->target_delta = 0.0; e->target_position = p->target_cutting_distance;
+    e->mode_error = 0;
+    e->n_sparks = e->n_short_us = e->n_short_events = e->crater_sum = e->n_pulse_short = 0.0;
+}
+
 int or_n_segments(const OrEnv *e) { return e->n; }
 void or_geometry(const OrEnv *e, int32_t out[5])
 {

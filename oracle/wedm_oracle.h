@@ -82,6 +82,7 @@ typedef struct OrEnv OrEnv;
 OrEnv *or_create(const OrParams *p);
 void or_destroy(OrEnv *e);
 void or_reset(OrEnv *e);                     /* fresh env semantics (all module state cleared) */
+void or_reset_reference(OrEnv *e);           /* the reference's own reset(): new EDMState only, module state survives */
 int or_n_segments(const OrEnv *e);
 void or_geometry(const OrEnv *e, int32_t out[5]); /* n, zone_start, zone_end, contact_bottom, contact_top */
 float *or_temperature(OrEnv *e);             /* live T field, n_segments floats */

@@ -41,7 +41,7 @@ _lib = None
 
 # every symbol include/sparc_b200.h declares
 EXPORTS = ("sparc_abi_version", "sparc_last_error", "sparc_num_fields", "sparc_field_info",
-           "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_reseed",
+           "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_reseed", "sparc_reset_reference",
            "sparc_params_bytes", "sparc_step",
            "sparc_step_injected", "sparc_step_ex", "sparc_step_logged", "sparc_step_sampled", "sparc_step_observe", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
            "sparc_step_host", "sparc_step_host_static", "sparc_static_max_envs", "sparc_host_action_pitch", "sparc_launch_info", "sparc_measure_fp32_peak")
@@ -69,6 +69,7 @@ def lib():
     L.sparc_init.argtypes = [vp, PP, i32, vp]
     L.sparc_reset.argtypes = [vp, PP, i32, vp, vp]
     L.sparc_reseed.argtypes = [vp, PP, i32, vp, vp]
+    L.sparc_reset_reference.argtypes = [vp, PP, i32, vp, vp]
     L.sparc_params_bytes.restype = sz
     L.sparc_step.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp]
     L.sparc_step_injected.argtypes = [vp, PP, PA, i32, i32, vp, vp]

@@ -111,6 +111,26 @@ __global__ void reset_kernel(const __grid_constant__ SparcParams P, SparcStatePt
     int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n_envs) return;
     if (mask && !mask[e]) return;
+    if (first_time == 3) {
+        // The REFERENCE's reset() (wire_edm.py:106-114): a new EDMState with workpiece_position = initial_gap; what the
+        // module objects keep on themselves survives: short-circuit countdowns and the current cache
+        // (ignition.py:75-83), prev_accel (mechanics.py:60), debris volume / flow condition / ion channel / hysteresis
+        // memory (dielectric.py:69-80), convection coefficients, flow memory and zone-mean cache (wire.py:204-225).
+        S.wp[e] = S.prm_initial_gap[e]; S.wire[e] = 0.0; S.v[e] = 0.0;
+        S.voltage[e] = 0.0; S.current[e] = 0.0;
+        S.target_voltage[e] = 0.0; S.on_time[e] = 0.0; S.off_time[e] = 0.0; S.target_delta[e] = 0.0;
+        S.unwind_v[e] = 0.2;
+        S.debris_density[e] = 0.0; S.cavity_volume[e] = 0.0; S.last_crater_volume[e] = 0.0;
+        S.spark_y[e] = -1.0; S.wire_avg_T[e] = 0.0;
+        S.stat_crater_sum[e] = 0.0; S.win_vsum[e] = 0.0;
+        S.time[e] = 0; S.t_servo[e] = 0; S.t_open_v[e] = 0; S.t_spark_ign[e] = 0; S.t_spark_end[e] = 0;
+        S.spark_state[e] = 0; S.spark_dur[e] = 0; S.crit_count[e] = 0; S.current_mode[e] = 0; S.flags[e] = 0;
+        S.stat_sparks[e] = 0; S.stat_short_us[e] = 0; S.stat_short_events[e] = 0; S.stat_pulse_short[e] = 0;
+        S.stat_steps[e] = 0; S.win_sparks[e] = 0; S.win_short_us[e] = 0; S.win_steps[e] = 0;
+        S.episode[e] = S.episode[e] + 1;
+        S.mech_prog[e] = 0;
+        return;
+    }
     if (first_time == 2) {                      // sparc_init: per-env parameters start as the engine's SparcParams
 #define X(name, ctype, dt) S.prm_##name[e] = (ctype)P.name;
         SPARC_ENV_PARAM_FIELDS(X)
@@ -478,6 +498,11 @@ int sparc_reset(void *state, const SparcParams *p, int n_envs, const uint8_t *ma
 int sparc_reseed(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream)
 {
     return do_reset(state, p, n_envs, mask_dev, stream, 1);
+}
+
+int sparc_reset_reference(void *state, const SparcParams *p, int n_envs, const uint8_t *mask_dev, void *stream)
+{
+    return do_reset(state, p, n_envs, mask_dev, stream, 3);
 }
 
 size_t sparc_params_bytes(void) { return sizeof(SparcParams); }

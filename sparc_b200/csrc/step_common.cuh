@@ -198,6 +198,7 @@ struct EnvState {
     uint32_t mech_ready;                         // pre-pass blocks known to be published
     uint32_t mech_self;                          // blocks this warp computed itself after a hand-off timeout
     bool ran_fast, zone_mean_written, cold_ok, convex, rng_valid, done;
+    bool ign_latched;        // IgnitionModule._cached_current_mode is not None (ignition.py:82-113): survives a reference-style reset
 };
 
 // Per-warp record in shared memory: the scalar state, the wire positions of the current 32-µs block
@@ -220,7 +221,9 @@ __device__ __forceinline__ void derive_generator(EnvState &s, const SparcParams 
     s.on_eff = (on != 0.0) ? on : s.q.default_on_time;
     s.onoff_eff = s.on_eff + ((off != 0.0) ? off : s.q.default_off_time);
     int mode = s.current_mode;
-    if (mode == 0) s.ipk = 60.0;
+    // None: the literal 60.0 A of a fresh module (ignition.py:83); once any mode was cached, None != cache sends it
+    // through the default mode instead (ignition.py:101-110) — only visible after a reference-style reset
+    if (mode == 0) s.ipk = s.ign_latched ? P.currents[s.q.default_current_mode] : 60.0;
     else s.ipk = P.currents[(mode < 1 || mode > SPARC_MAX_MODE) ? s.q.default_current_mode : mode];
     // smallest integer duration d with (double)d >= onoff_eff (rest -> idle, ignition.py:307-309)
     double c = ceil(s.onoff_eff);
@@ -419,6 +422,8 @@ __device__ __noinline__ void general_pre(EnvState &s, const SparcParams &P, cons
         const int a_mode = a.act.current_mode[e];
         s.target_delta = s.delta_new0;                      // act.servo[e] or the in-kernel controller's command
         s.current_mode = (a_mode == 0) ? -1 : a_mode;       // "I0" is a string, not None
+        s.ign_latched = true;                               // the next _get_current_from_mode() caches a mode
+        if (s.writer) S.ign_cached_mode[e] = (a_mode < 1 || a_mode > SPARC_MAX_MODE) ? s.q.default_current_mode : a_mode;
         derive_generator(s, P, a_tv, a_on, a_off);
         if (s.writer) { S.target_voltage[e] = a_tv; S.on_time[e] = a_on; S.off_time[e] = a_off; }
         s.latch_time = s.time;

@@ -335,6 +335,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     s.heat_on = false; s.thermal = false; s.refresh = false; s.freeze = false; s.became_done = false;
     s.jA = 0.f; s.jB = 0.f; s.fP = 0.f; s.hb = 0.f; s.he = 0.f;
     s.gap_lo_f = 0.0; s.gap_hi_f = -1.0; s.lo_c = 0.0; s.hi_c = 0.0; s.flush_amt = 0.0; s.onoff_thr = 0;
+    s.ign_latched = S.ign_cached_mode[e] != 0;
     derive_generator(s, P, S.target_voltage[e], S.on_time[e], S.off_time[e]);
     s.wp = S.wp[e]; s.wire = S.wire[e]; s.v = S.v[e]; s.prev_accel = S.prev_accel[e];
     s.fin_wire = s.wire; s.fin_v = s.v; s.fin_pa = s.prev_accel;

@@ -86,14 +86,15 @@ class Engine:
         N.check(self.lib.sparc_launch_info(self.n_envs, self.n_segments, out))
         return dict(lanes_per_env=out[0], cells_per_lane=out[1], block_threads=out[2], blocks=out[3])
 
-    def reset(self, mask: Optional[torch.Tensor] = None, reseed: bool = False) -> None:
+    def reset(self, mask: Optional[torch.Tensor] = None, reseed: bool = False, reference_semantics: bool = False) -> None:
         """Fresh-env state for the masked envs (all when mask is None).  Each reset starts a new
         episode (a new Philox stream); `reseed=True` — the caller passed a seed — starts the episode
         counter over, so that `reset(seed=s)` replays the same episode every time."""
         m = None
         if mask is not None:
             m = mask.to(device=self.device, dtype=torch.uint8).contiguous()
-        fn = self.lib.sparc_reseed if reseed else self.lib.sparc_reset
+        # reference_semantics: only EDMState is re-created, module-internal state survives (sparc_reset_reference)
+        fn = self.lib.sparc_reset_reference if reference_semantics else (self.lib.sparc_reseed if reseed else self.lib.sparc_reset)
         with torch.cuda.device(self.device):
             N.check(fn(self.blob.data_ptr(), C.byref(self.params), self.n_envs, _ptr(m), self._stream()))
 

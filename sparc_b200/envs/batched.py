@@ -38,7 +38,7 @@ class BatchedWireEDMEnv:
                  wire_params: WireModuleParameters = None, material_params: MaterialModuleParameters = None,
                  dielectric_params: DielectricModuleParameters = None,
                  mechanics_params: MechanicsModuleParameters = None, seed: int = 0, env_id_base: int = 0,
-                 latch_first_action: bool = True, auto_reset: bool = False):
+                 latch_first_action: bool = True, auto_reset: bool = False, strict_reference_reset: bool = False):
         if mechanics_control_mode not in ["position", "velocity"]:
             raise ValueError(f"mechanics_control_mode must be 'position' or 'velocity', got {mechanics_control_mode}")
         self.config = config or EnvironmentConfig()
@@ -49,6 +49,9 @@ class BatchedWireEDMEnv:
         self.dt = self.config.dt
         self.latch_first_action = bool(latch_first_action)
         self.auto_reset = bool(auto_reset)
+        # False (default): reset() gives the state of a freshly CONSTRUCTED env.  True: the reference's own reset(), which
+        # re-creates only EDMState and lets module-internal state survive into the next episode
+        self.strict_reference_reset = bool(strict_reference_reset)
         self._module_params = dict(ignition=ignition_params, wire=wire_params, material=material_params,
                                    dielectric=dielectric_params, mechanics=mechanics_params)
         self.params = derive_params(self.config, mechanics_control_mode, ignition_params, wire_params,
@@ -80,7 +83,7 @@ class BatchedWireEDMEnv:
         """Fresh-env state for all envs (or the masked ones).  A seed re-keys the Philox streams."""
         if seed is not None:
             self.engine.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
-        self.engine.reset(mask, reseed=seed is not None)
+        self._reset_engine(mask, seed is not None)
         self._arm_latch(mask)
         return self._obs(), {}
 
@@ -122,6 +125,15 @@ class BatchedWireEDMEnv:
         idx = torch.as_tensor(env_ids, device=self.device, dtype=torch.long).reshape(-1)
         for name in per_env:
             self.engine["prm_" + name][idx] = getattr(p, name)
+
+    def _reset_engine(self, mask, reseed: bool):
+        self.engine.reset(mask, reseed=reseed, reference_semantics=self.strict_reference_reset)
+        if self.strict_reference_reset and reseed:          # a seeded reset replays the same Philox episode
+            ep = self.engine["episode"]
+            if mask is None:
+                ep.zero_()
+            else:
+                ep[mask.to(self.device).bool()] = 0
 
     def _stage(self, actions: Dict):
         gc = actions["generator_control"]
@@ -180,7 +192,7 @@ class BatchedWireEDMEnv:
         truncated = torch.zeros(self.n_envs, dtype=torch.bool, device=self.device)
         if self.auto_reset:
             info["final_terminated"] = terminated.clone()
-            self.engine.reset(terminated)
+            self._reset_engine(terminated, False)
             self._arm_latch(terminated)
         return obs, reward, terminated, truncated, info
 

@@ -32,9 +32,12 @@ class WireEDMEnv(EnvBase):
                  config: EnvironmentConfig = None, ignition_params: IgnitionModuleParameters = None,
                  wire_params: WireModuleParameters = None, material_params: MaterialModuleParameters = None,
                  dielectric_params: DielectricModuleParameters = None,
-                 mechanics_params: MechanicsModuleParameters = None, device="cuda:0"):
+                 mechanics_params: MechanicsModuleParameters = None, device="cuda:0",
+                 strict_reference_reset: bool = False):
         super().__init__()
         self.render_mode = render_mode
+        # True: reset() keeps module-internal state like the reference does; default: a fresh env
+        self.strict_reference_reset = bool(strict_reference_reset)
         if mechanics_control_mode not in ["position", "velocity"]:
             raise ValueError(f"mechanics_control_mode must be 'position' or 'velocity', got {mechanics_control_mode}")
         self.mechanics_control_mode = mechanics_control_mode
@@ -78,7 +81,9 @@ class WireEDMEnv(EnvBase):
         if seed is not None:
             self.np_random = np.random.default_rng(seed)
             self._engine.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
-        self._engine.reset(None, reseed=seed is not None)
+        self._engine.reset(None, reseed=seed is not None, reference_semantics=self.strict_reference_reset)
+        if self.strict_reference_reset and seed is not None:
+            self._engine["episode"].zero_()
         self._bind()
         return self._get_obs(), {}
 

@@ -284,3 +284,46 @@ def test_signal_log_matches_reference_golden(name):
     assert checked >= 3000
     # the per-call window spans the whole call even though it was cut into launches at the samples
     assert int(eng["win_steps"][0].item()) == 1000 or int(eng["flags"][0].item()) & N.F_DONE
+
+
+def test_strict_reference_reset_matches_reference_golden():
+    """`strict_reference_reset=True`: reset() clears only what the reference's reset() clears (a new EDMState); the
+    module-internal state — short-circuit countdown, debris volume, hysteresis and convection memory, prev_accel —
+    survives.  Second episode of the unmodified reference (tests/golden/reference_reset.npz) µs by µs for the first
+    150 µs (the carried countdown), then per 1000-µs launch."""
+    import torch
+    from sparc_b200 import (BatchedWireEDMEnv, DielectricModuleParameters, EnvironmentConfig, IgnitionModuleParameters)
+
+    g = _golden("reference_reset")
+    case = CS.CASES["debris_shorts"]
+    n1, n2 = int(g["n1"][0]), int(g["n2"][0])
+    env = BatchedWireEDMEnv(3, config=EnvironmentConfig(**case["config"]), ignition_params=IgnitionModuleParameters(**case["ignition"]),
+                            dielectric_params=DielectricModuleParameters(**case["dielectric"]), latch_first_action=False,
+                            strict_reference_reset=True)
+    eng = env.engine
+    t1 = torch.from_numpy(np.stack([CS.make_tape(4101, n1)] * 3)).to(eng.device)
+    t2 = torch.from_numpy(np.stack([CS.make_tape(4102, 4000)] * 3)).to(eng.device)
+    done = 0
+    for n in (1000, 1000, 1000, n1 - 3000):
+        PU.stage_action(eng, PU.action_for_window(g["actions1"], done, n))
+        eng.step(n, t1[:, done:done + n].contiguous())
+        done += n
+    assert float(eng["debris_volume"][0]) > 1e-4 and int(eng["deb_short_rem"][0]) + int(eng["rand_short_rem"][0]) > 0
+    env.reset()                                        # reference semantics: EDMState only
+    assert int(eng["time"][0]) == 0 and float(eng["debris_volume"][0]) > 1e-4
+    done, checked = 0, 0
+    plan = [1] * 150 + [850] + [1000] * ((n2 - 1000) // 1000)
+    for n in plan:
+        PU.stage_action(eng, PU.action_for_window(g["actions2"], done, n))
+        eng.step(n, t2[:, done:done + n].contiguous())
+        done += n
+        f, i = PU.read_rows(eng, envs=(0, 2))
+        for row in range(2):
+            PU.assert_rows_match(f[row], i[row], g["f64"][done - 1], g["i32"][done - 1].astype(np.int64),
+                                 where=f"strict reset, episode 2 after {done} µs")
+        checked += 1
+        if done % 1000 == 0:
+            T_ref = g["T"][done // 1000 - 1]
+            err = np.abs(eng.T[0].cpu().numpy().astype(np.float64) - T_ref.astype(np.float64))
+            assert np.all(err <= PU.T_ATOL + PU.T_RTOL * np.abs(T_ref))
+    assert checked >= 150 and done == n2

@@ -67,3 +67,31 @@ def test_philox_known_answer():
     assert [hex(x) for x in out] == ["0x408f276d", "0x41c83b0e", "0xa20bc7c6", "0x6d5451fd"]
     out = O.philox4x32_10([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0])
     assert [hex(x) for x in out] == ["0xd16cfe09", "0x94fdcceb", "0x5001e420", "0x24126ea1"]
+
+
+def test_oracle_reference_style_reset_matches_reference_golden():
+    """strict_reference_reset: a second episode on USED modules.  The golden holds the UNMODIFIED
+    reference's second episode after RESET_N1 µs of the debris_shorts case and a plain `env.reset()`
+    (oracle/validate_oracle.py::check_reference_reset); the oracle's `reset(reference_semantics=True)` must
+    reproduce it bit for bit — the short-circuit countdown and the debris volume carry over."""
+    import numpy as np
+    from oracle import cases as CS
+    from oracle import oracle as O
+
+    g = np.load(os.path.join(GOLDEN_DIR, "reference_reset.npz"))
+    case = CS.CASES["debris_shorts"]
+    n1, n2 = int(g["n1"][0]), int(g["n2"][0])
+    e = O.OracleEnv(**CS.oracle_overrides(case))
+    e.run(n1, g["actions1"], draws=CS.make_tape(4101, n1), rec_every=0)
+    e.reset(reference_semantics=True)
+    res = e.run(n2, g["actions2"], draws=CS.make_tape(4102, 4000), rec_every=1, t_every=1000)
+    assert np.array_equal(res["i32"], g["i32"].astype(res["i32"].dtype))
+    assert np.array_equal(res["f64"], g["f64"])
+    assert np.array_equal(res["T"], g["T"])
+    assert g["i32"][:100, 6].sum() > 50 and g["f64"][0, 6] > 1e-4      # carried short circuit and debris
+    # a fresh-env reset gives a different second episode
+    e2 = O.OracleEnv(**CS.oracle_overrides(case))
+    e2.run(n1, g["actions1"], draws=CS.make_tape(4101, n1), rec_every=0)
+    e2.reset()
+    res2 = e2.run(n2, g["actions2"], draws=CS.make_tape(4102, 4000), rec_every=1)
+    assert not np.array_equal(res2["i32"][:100], g["i32"][:100])
