@@ -392,7 +392,7 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
             size_t dyn = 0;
             if (tlog || signals) {
                 const size_t n_stage = ((size_t)p->n_segments + 3) & ~(size_t)3;
-                dyn = 2 * n_stage * sizeof(float) * (v->W == 1 ? SPARC_BLOCK_THREADS / 32 : 1);
+                dyn = (size_t)SPARC_LOG_NBUF(v->W) * n_stage * sizeof(float) * (v->W == 1 ? SPARC_BLOCK_THREADS / 32 : 1);
                 if (dyn > 40 * 1024) CUDA_TRY(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
             }
             cfg.dynamicSmemBytes = dyn;

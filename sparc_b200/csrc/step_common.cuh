@@ -130,6 +130,9 @@ __device__ __forceinline__ double servo_command(const StepArgs &a, const SparcSt
     return (double)a.act.servo[e];
 }
 
+// staging buffers per env of the LOG kernels: block-per-env variants keep two row copies in flight
+#define SPARC_LOG_NBUF(W) ((W) > 1 ? 3 : 2)
+
 #ifndef SPARC_BLOCK_THREADS
 #define SPARC_BLOCK_THREADS 64      /* W == 1: two envs per block */
 #endif

@@ -5,9 +5,9 @@
 namespace sparc {
 static const StepVariant kTable[] = {
 #ifdef SPARC_QUICK   /* experiments: one variant per W, compiles in seconds */
-    SPARC_STEP_VARIANT(16, 2),
+    SPARC_STEP_VARIANT(18, 2),
 #else
-    SPARC_STEP_VARIANT(16, 2), SPARC_STEP_VARIANT(20, 2), SPARC_STEP_VARIANT(24, 2),
+    SPARC_STEP_VARIANT(18, 2), SPARC_STEP_VARIANT(22, 2), SPARC_STEP_VARIANT(26, 2),
 #endif
 };
 const StepVariant *step_variants_w2(int *n)

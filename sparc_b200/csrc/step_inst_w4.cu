@@ -5,9 +5,9 @@
 namespace sparc {
 static const StepVariant kTable[] = {
 #ifdef SPARC_QUICK   /* experiments: one variant per W, compiles in seconds */
-    SPARC_STEP_VARIANT(16, 4),
+    SPARC_STEP_VARIANT(18, 4),
 #else
-    SPARC_STEP_VARIANT(16, 4), SPARC_STEP_VARIANT(20, 4), SPARC_STEP_VARIANT(24, 4),
+    SPARC_STEP_VARIANT(18, 4), SPARC_STEP_VARIANT(22, 4), SPARC_STEP_VARIANT(26, 4),
 #endif
 };
 const StepVariant *step_variants_w4(int *n)

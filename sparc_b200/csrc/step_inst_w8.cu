@@ -5,9 +5,9 @@
 namespace sparc {
 static const StepVariant kTable[] = {
 #ifdef SPARC_QUICK   /* experiments: one variant per W, compiles in seconds */
-    SPARC_STEP_VARIANT(16, 8),
+    SPARC_STEP_VARIANT(18, 8),
 #else
-    SPARC_STEP_VARIANT(16, 8), SPARC_STEP_VARIANT(20, 8), SPARC_STEP_VARIANT(24, 8),
+    SPARC_STEP_VARIANT(18, 8), SPARC_STEP_VARIANT(22, 8), SPARC_STEP_VARIANT(26, 8),
 #endif
 };
 const StepVariant *step_variants_w8(int *n)

@@ -483,39 +483,56 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     const int log_rows = logging ? a.total_us / a.log_every : 0;
     int log_ctr = logging ? a.log_every - a.it_base % a.log_every : 0;  // µs until the next sample
     int log_row = logging ? a.it_base / a.log_every : 0;                // next row to write
-    // Row staging for the log (LOG kernels only; dynamic shared memory): two buffers of n_stage floats per env,
+    // Row staging for the log (LOG kernels only; dynamic shared memory): NBUF buffers of n_stage floats per env,
     // the whole row in cell order.  When the rows are 16-byte aligned in the log (N % 4 == 0) a row leaves as ONE
     // bulk asynchronous copy shared -> global (cp.async.bulk, SASS UBLKCP) issued by one thread, double buffered
     // so that the next µs's stencil does not wait for it; otherwise as coalesced 4-byte stores.
     const int n_stage = (N + 3) & ~3;
-    float *stage0 = sm_stage + (size_t)((W == 1) ? wib : 0) * 2 * n_stage;
+    constexpr int NBUF = SPARC_LOG_NBUF(W);    // staging buffers per env (host: same macro)
+    float *stage0 = sm_stage + (size_t)((W == 1) ? wib : 0) * NBUF * n_stage;
     const bool bulk_rows = (N % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.tlog) & 15u) == 0);
     int log_buf = 0;
     auto group_sync = [&]() { if constexpr (W > 1) __syncthreads(); else __syncwarp(); };
+    // shared-memory byte addresses of this lane's two halves inside staging buffer 0 (buffer 1 is n_stage floats on)
+    const uint32_t st_x = (uint32_t)__cvta_generic_to_shared(stage0) + 4u * (uint32_t)geom.cx0;
+    const uint32_t st_y = (uint32_t)__cvta_generic_to_shared(stage0) + 4u * (uint32_t)geom.cy0;
     auto write_log_row = [&](int r) {
-        float *row = a.tlog + ((size_t)e * log_rows + r) * N;
-        float *stage = stage0 + log_buf * n_stage;
-        if (bulk_rows) {
-            // the bulk copy issued two rows ago has finished READING this buffer
-            if (gl == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+        const uint32_t boff = 4u * (uint32_t)(log_buf * n_stage);
+        if (bulk_rows && W == 1) {
+            // the bulk copy issued two rows ago has finished READING this buffer (W > 1: the issuing thread waited
+            // right after its last commit, and every thread has passed a halo barrier since)
+            if (gl == 0) asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(NBUF - 1) : "memory");
             group_sync();
         }
+        // one base register per half, immediate offsets (the generic form recomputed every address and every
+        // `j < n` predicate: 3 instructions per stored cell, profiles/r02_experiments.txt §6)
+        if (!lf.empty_x) {
+            const uint32_t ax = st_x + boff;
 #pragma unroll
-        for (int j = 0; j < H; j++) {
-            if (j < geom.nx) stage[geom.cx0 + j] = T[j].x;
-            if (j < geom.ny) stage[geom.cy0 + j] = T[j].y;
+            for (int j = 0; j < H - 1; j++) asm volatile("st.shared.f32 [%0], %1;" :: "r"(ax + 4u * j), "f"(T[j].x) : "memory");
+            if (!lf.short_x) asm volatile("st.shared.f32 [%0], %1;" :: "r"(ax + 4u * (H - 1)), "f"(T[H - 1].x) : "memory");
         }
+        if (!lf.empty_y) {
+            const uint32_t ay = st_y + boff;
+#pragma unroll
+            for (int j = 0; j < H - 1; j++) asm volatile("st.shared.f32 [%0], %1;" :: "r"(ay + 4u * j), "f"(T[j].y) : "memory");
+            if (!lf.short_y) asm volatile("st.shared.f32 [%0], %1;" :: "r"(ay + 4u * (H - 1)), "f"(T[H - 1].y) : "memory");
+        }
+        float *stage = stage0 + log_buf * n_stage;
         if (gl == 0) stage[0] = spoolf;
         if (bulk_rows) {
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> async proxy
             group_sync();
             if (gl == 0) {
+                float *row = a.tlog + ((size_t)e * log_rows + r) * N;          // only the issuing thread needs it
                 const uint32_t src = (uint32_t)__cvta_generic_to_shared(stage);
                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;\n\tcp.async.bulk.commit_group;"
                              :: "l"(row), "r"(src), "r"((uint32_t)(N * 4)) : "memory");
+                if (W > 1) asm volatile("cp.async.bulk.wait_group.read %0;" :: "n"(NBUF - 1) : "memory");   // frees the NEXT buffer
             }
-            log_buf ^= 1;
+            log_buf = (log_buf + 1 == NBUF) ? 0 : log_buf + 1;
         } else {
+            float *row = a.tlog + ((size_t)e * log_rows + r) * N;
             group_sync();
             for (int c = ((W == 1) ? lane : (int)threadIdx.x); c < N; c += 32 * W) row[c] = stage[c];
             group_sync();
