@@ -189,11 +189,11 @@ __device__ __forceinline__ void stencil_quiet_us(float2 (&T)[H], const Coefs<H, 
 
 // n quiet µs.  HOT additionally runs _check_wire_breaking (wire.py:376-388) every µs and returns the
 // number of µs executed (n, or k+1 when the wire broke on µs k; `broke` says which).
-template <int H, bool HOT, bool ALIGNED, int W, bool LOG, class LogTick>
+template <int H, bool HOT, bool ALIGNED, int W, bool LOG, class LogTick, class SigCap>
 __device__ __forceinline__ int run_quiet(float2 (&T)[H], const Coefs<H, ALIGNED> &co, const float cRf, const float ncL,
                                          const float spoolf, const LaneFlags &f, EnvCtx<W> &ctx, const int n,
                                          const float crit_T, const float break_T, int &crit_count, bool &broke,
-                                         bool &cold_after, LogTick &&log_tick)
+                                         bool &cold_after, LogTick &&log_tick, SigCap &&sig_cap)
 {
     const float2 ncL2 = make_float2(ncL, ncL), cR2 = make_float2(cRf, cRf);
     const float gate_T = fminf(crit_T, break_T);
@@ -227,6 +227,7 @@ __device__ __forceinline__ int run_quiet(float2 (&T)[H], const Coefs<H, ALIGNED>
             if (brk) { broke = true; return k + 1; }
             if (k == n - 1) cold_after = !vote_any<W>(lmax > gate_T - 1.0f);
         }
+        if (LOG) sig_cap(k, HOT ? crit_count : 0);   // sampled signals: this µs's max temperature / critical count
     }
     if (!HOT) crit_count = 0;
     return n;
@@ -539,6 +540,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
         }
     };
     auto log_tick = [&]() {                     // called after every thermal update of a logged env
+        if (!logging) return;
         if (--log_ctr == 0) {
             if (log_row < log_rows) write_log_row(log_row);
             log_row += 1;
@@ -549,14 +551,24 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     // per-signal log (SimulationLogger scalar signals, utils/logger.py:105-160): row r of the CALL holds what the
     // reference's `getattr(state, name)` returns after µs (r+1)*sample_every - 1.  Written by this kernel: quiet runs
     // are cut at the sampling µs, the lazily kept dielectric state is read through dielectric_view().
+    __shared__ float sm_cap[(LOG && W > 1) ? W : 1][32];   // W > 1: per-warp maxima of a run's µs, combined after the run
     const bool sig_on = LOG && a.signals != nullptr && a.sample_every > 0;
     const int sig_rows = sig_on ? a.total_us / a.sample_every : 0;
-    int sig_ctr = sig_on ? a.sample_every - a.it_base % a.sample_every : 0;  // µs until the next sample
-    int sig_row = sig_on ? a.it_base / a.sample_every : 0;
+    int done_idx = 0;                           // launch-µs index of the terminating µs (rows from there on: final state)
+    float cap_max = spoolf;                     // quiet runs: lane i + k keeps µs k's max temperature (this warp's cells)
+    int cap_crit = 0;                           //             and time_in_critical_temp after it
+    int cap_base = 0;                           // block index of the run's first µs
+    int cap_ctr = 1;                            // µs until the next sampled µs of the run (1 = the next one)
+    auto sig_cap = [&](int k, int crit) {
+        if (!(LOG && sig_on)) return;
+        if (--cap_ctr != 0) return;             // not a sampled µs
+        cap_ctr = a.sample_every;
+        // temperatures are positive: unsigned order of the bit patterns is float order -> one REDUX instruction
+        const float m = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(lane_max<H>(T, lf, spoolf))));
+        if (lane == cap_base + k) { cap_max = m; cap_crit = crit; }
+    };
     auto env_max_T = [&]() {                    // max over the env's cells; every thread of the env calls it
-        float m = lane_max<H>(T, lf, spoolf);   // cell 0 is spoolf
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
+        float m = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(lane_max<H>(T, lf, spoolf))));   // cell 0 is spoolf
         if constexpr (W > 1) {
             __syncthreads();
             if (lane == 0) sm_red[ctx.wid] = (double)m;
@@ -587,15 +599,15 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
         row[SPARC_SIG_TIME_IN_CRITICAL * ne] = (double)crit;
         row[SPARC_SIG_FLAGS * ne] = (double)flags;
     };
-    auto sig_emit = [&](double wire, double v) { // the state after the µs just executed (not terminated)
+    auto sig_emit = [&](int launch_us, double wire, double v) { // the state after launch-µs `launch_us` (a general µs)
+        const int cu = a.it_base + launch_us + 1;
+        if (cu % a.sample_every != 0) return;                // uniform over the env
         const float m = env_max_T();
         double dens, vol;
         dielectric_view(s, P, dens, vol);
         const int st = s.spark_state;
-        sig_write(sig_row, (double)s.time, s.voltage, (st == 1 || st == -1) ? s.ipk : 0.0, wire, v, dens, vol, s.flags, st, m,
-                  s.avg_view, s.crit_count);
-        sig_row += 1;
-        sig_ctr = a.sample_every;
+        sig_write(cu / a.sample_every - 1, (double)s.time, s.voltage, (st == 1 || st == -1) ? s.ipk : 0.0, wire, v, dens, vol,
+                  s.flags, st, m, s.avg_view, s.crit_count);
     };
 
     // mechanics pre-pass results of this launch (mech_kernel).  The pre-pass is STILL RUNNING while this
@@ -638,7 +650,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
 #ifdef SPARC_ABL_ALLQUIET
     {   // ablation: the whole launch as ONE cold quiet run (stencil speed inside this kernel)
         bool broke = false, cold_after = true; int cc = 0;
-        run_quiet<H, false, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, a.n_us, 0.f, 0.f, cc, broke, cold_after, log_tick);
+        run_quiet<H, false, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, a.n_us, 0.f, 0.f, cc, broke, cold_after, log_tick, sig_cap);
         s.time += a.n_us; it = a.n_us; need_mech(a.n_us);
     }
 #endif
@@ -685,8 +697,6 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             __syncwarp();
             R.vel[lane + 1] = __ldcg(S.mech_trajv + (size_t)e * SPARC_MECH_EPOCH + it + ((lane < nb) ? lane : nb - 1));
         }
-        unsigned stop_cache = 0;                // LOG: the look-ahead's stop mask of this block, valid while runs are
-        bool stop_ok = false;                   // only cut at sampling µs (nothing it depends on has changed)
         const int blk_time = s.time;
         // ignition rolls (slot 2): word t&3 of Philox block t>>2; each lane computes one counter of a
         // 32-counter window and keeps all four words: one refill serves 125..128 µs
@@ -707,18 +717,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             int n = 0;
             int off_tr = -1;                    // run offset of the rest -> idle transition µs
             const int spark_state = s.spark_state;
-            bool from_cache = false;
-            if (LOG && stop_ok && !force_general && !((stop_cache >> i) & 1u)) {
-                // the previous run was cut at a sampling µs, not by a stop: the mask still holds
-                const unsigned stop = stop_cache >> i;
-                n = stop ? __ffs(stop) - 1 : 32 - i;
-                if (spark_state == -2) {
-                    off_tr = s.onoff_thr - s.spark_dur - 1;
-                    if (off_tr < 0) off_tr = 0;
-                }
-                from_cache = true;
-            }
-            if (!from_cache && !force_general && s.fast_ok && (spark_state == 0 || spark_state == -2)) {
+            if (!force_general && s.fast_ok && (spark_state == 0 || spark_state == -2)) {
                 const double pre_l = R.pos[lane], post_l = R.pos[lane + 1];
                 const double wp = s.wp, debris_volume = s.debris_volume;
                 const double g = wp - pre_l;
@@ -760,9 +759,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                         ok = ok && (den > 0.0 && u3 * den > SPARC_LN2_UP);
                     }
                 }
-                unsigned stop = __ballot_sync(FULL, !(ok && in_band()));
-                if (LOG) { stop_cache = stop; stop_ok = true; }
-                stop >>= i;
+                unsigned stop = __ballot_sync(FULL, !(ok && in_band())) >> i;
                 n = stop ? __ffs(stop) - 1 : 32 - i;
                 if (n == 0 && ((__ballot_sync(FULL, ok) >> i) & 1u)) {
                     // only a band failed on µs i: refresh the hysteresis state in place (light_refresh)
@@ -776,39 +773,84 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                             double deb_lo = dv2;
                             if (dv2 > 0.001) deb_lo = dv2 - (double)(off + 1) * s.flush_amt - 1e-14;
                             b = b && deb_lo >= s.lo_c * g && dv2 <= s.hi_c * g;
-                            stop = __ballot_sync(FULL, !(ok && b));
-                            if (LOG) { stop_cache = stop; stop_ok = true; }
-                            stop >>= i;
+                            stop = __ballot_sync(FULL, !(ok && b)) >> i;
                             n = stop ? __ffs(stop) - 1 : 32 - i;
                         }
                     }
                 }
             }
             force_general = false;
-            if (LOG && sig_on && n > sig_ctr) n = sig_ctr;      // a sampling µs is always the last µs of a run
 
             if (n > 0) {
                 // ================= quiet run ===================================================
                 bool broke = false, cold_after = s.cold_ok;
                 int nx, crit_count = s.crit_count;
+                cap_base = i;
+                if (LOG && sig_on) cap_ctr = a.sample_every - (a.it_base + it + i) % a.sample_every;
                 const bool cold = s.cold_ok && s.convex;
-                if (!LOG || !logging) {
+                if (!LOG || !(logging || sig_on)) {
                     if (cold)
                         nx = run_quiet<H, false, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, n, 0.f, 0.f, crit_count,
-                                                                    broke, cold_after, log_tick);
+                                                                    broke, cold_after, log_tick, sig_cap);
                     else
                         nx = run_quiet<H, true, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, n, P.critical_temperature_f32,
-                                                                   P.breaking_temperature_f32, crit_count, broke, cold_after, log_tick);
+                                                                   P.breaking_temperature_f32, crit_count, broke, cold_after, log_tick, sig_cap);
                 } else {
                     if (cold)
                         nx = run_quiet<H, false, ALIGNED, W, LOG>(T, co, cRf, ncL, spoolf, lf, ctx, n, 0.f, 0.f, crit_count, broke,
-                                                                  cold_after, log_tick);
+                                                                  cold_after, log_tick, sig_cap);
                     else
                         nx = run_quiet<H, true, ALIGNED, W, LOG>(T, co, cRf, ncL, spoolf, lf, ctx, n, P.critical_temperature_f32,
-                                                                 P.breaking_temperature_f32, crit_count, broke, cold_after, log_tick);
+                                                                 P.breaking_temperature_f32, crit_count, broke, cold_after, log_tick, sig_cap);
                 }
                 s.crit_count = crit_count;
                 s.cold_ok = cold_after;
+                if (LOG && sig_on) {
+                    // signal rows of this run, one µs per lane (lane i + l owns run offset l), from the state BEFORE the
+                    // bookkeeping below: what the reference holds after each of these quiet step() calls
+                    float m_l = cap_max;
+                    if constexpr (W > 1) {      // combine the warps' per-µs maxima
+                        sm_cap[ctx.wid][lane] = cap_max;
+                        __syncthreads();
+#pragma unroll
+                        for (int w = 0; w < W; w++) m_l = fmaxf(m_l, sm_cap[w][lane]);
+                        __syncthreads();
+                    }
+                    const int l = lane - i, n_rows = broke ? nx - 1 : nx;       // the breaking µs: final state (done path)
+                    const int cu = a.it_base + it + lane + 1;
+                    if (ctx.wid == 0 && l >= 0 && l < n_rows && cu % a.sample_every == 0 && cu / a.sample_every - 1 < sig_rows) {
+                        const bool idle_l = (spark_state == 0) || l >= off_tr;   // rest -> idle on run offset off_tr
+                        const int flags_l = (spark_state == -2 && l >= off_tr) ? (s.flags & ~SPARC_F_HAS_Y) : s.flags;
+                        const double fa = s.flush_amt;
+                        double u = s.debris_volume;                              // volume before the pending flush
+                        const int n_before = l + 1 - s.skip_flush;               // flushes applied before µs l's density
+                        for (int t = 0; t < n_before; t++) if (fa > 0.0 && u > 0.001) u = u - fa;
+                        const double gl_ = s.wp - R.pos[lane];
+                        const double gq = (gl_ > 0.001) ? gl_ : 0.001;
+                        const double cavity = P.cavity_volume_coeff * (gq * 0.001);
+                        double dens = 0.0;
+                        if (cavity > 0.0) { const double d = u / cavity; dens = (d < 1.0) ? d : 1.0; }
+                        const double vol = (fa > 0.0 && u > 0.001) ? u - fa : u;
+                        const size_t ne = (size_t)a.n_envs;
+                        double *row = a.signals + (size_t)(cu / a.sample_every - 1) * SPARC_N_SIGNALS * ne + e;
+                        row[SPARC_SIG_TIME * ne] = (double)(s.time + l + 1);
+                        row[SPARC_SIG_VOLTAGE * ne] = idle_l ? s.tv_eff : 0.0;
+                        row[SPARC_SIG_CURRENT * ne] = 0.0;
+                        row[SPARC_SIG_WIRE_POSITION * ne] = R.pos[lane + 1];
+                        row[SPARC_SIG_WIRE_VELOCITY * ne] = R.vel[lane + 1];
+                        row[SPARC_SIG_WORKPIECE_POSITION * ne] = s.wp;
+                        row[SPARC_SIG_TARGET_DELTA * ne] = s.target_delta;
+                        row[SPARC_SIG_DEBRIS_DENSITY * ne] = dens;
+                        row[SPARC_SIG_FLOW_RATE * ne] = s.flow;
+                        row[SPARC_SIG_IS_SHORT_CIRCUIT * ne] = 0.0;
+                        row[SPARC_SIG_SPARK_STATE * ne] = idle_l ? 0.0 : -2.0;
+                        row[SPARC_SIG_MAX_TEMPERATURE * ne] = (double)m_l;
+                        row[SPARC_SIG_AVERAGE_TEMPERATURE * ne] = s.avg_view;
+                        row[SPARC_SIG_DEBRIS_VOLUME * ne] = vol;
+                        row[SPARC_SIG_TIME_IN_CRITICAL * ne] = (double)cap_crit;
+                        row[SPARC_SIG_FLAGS * ne] = (double)flags_l;
+                    }
+                }
                 // scalar bookkeeping of the nx quiet µs (ignition.py:302-319, dielectric.py:104-144)
                 int n_idle = nx;
                 if (spark_state == -2) {
@@ -838,20 +880,16 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                     s.tsi_break = 0;
                     s.done = true;
                     s.time += nx - 1;
+                    done_idx = it + i + nx - 1;
                     rewind_mech(it + i + nx - 1);
                     break;
                 }
                 s.time += nx;
                 i += nx;
-                if (LOG && sig_on) {
-                    sig_ctr -= nx;
-                    if (sig_ctr == 0) sig_emit(R.pos[i], R.vel[i]);
-                }
                 continue;
             }
 
             // ================= general µs ======================================================
-            stop_ok = false;
             s.wire = R.pos[i];
             s.it = it + i;
             if (s.ran_fast) { s.dens_valid = false; s.pend_flush = true; s.ran_fast = false; }
@@ -861,6 +899,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             if (s.refresh) refresh_coeffs(s.hb, s.he);
             if (s.freeze) {                     // crater-table miss: frozen before the thermal update
                 s.done = true;
+                done_idx = it + i;
                 rewind_mech(it + i);
                 break;
             }
@@ -954,6 +993,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                 s.flags |= SPARC_F_BROKEN | SPARC_F_THERMAL_BREAK;
                 s.tsi_break = s.tsi_prev;
                 s.done = true;
+                done_idx = it + i;
                 rewind_mech(it + i);
                 break;
             }
@@ -963,12 +1003,9 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             // ---- _check_termination (wire_edm.py:172-179) -------------------------------------
             if (R.pos[i + 1] > s.wp + 100.0) { s.flags |= SPARC_F_BROKEN; s.done = true; }
             else if (s.wp >= s.q.target_position) { s.flags |= SPARC_F_TARGET; s.done = true; }
-            if (s.done) { rewind_mech(it + i + 1); break; }
+            if (s.done) { done_idx = it + i; rewind_mech(it + i + 1); break; }
             i += 1;
-            if (LOG && sig_on) {
-                sig_ctr -= 1;
-                if (sig_ctr == 0) sig_emit(R.pos[i], R.vel[i]);
-            }
+            if (LOG && sig_on) sig_emit(it + i - 1, R.pos[i], R.vel[i]);
         }
         it += nb;
     }
@@ -1054,16 +1091,14 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
         if (gl == 0) {
             const int st = s.spark_state;
             const double avg = S.wire_avg_T[e];
-            for (int r = sig_row; r < sig_rows; r++)
+            for (int r = (a.it_base + done_idx) / a.sample_every; r < sig_rows; r++)
                 sig_write(r, (double)s.time, s.voltage, (st == 1 || st == -1) ? s.ipk : 0.0, s.fin_wire, s.fin_v, s.debris_density,
                           s.debris_volume, s.flags, st, m, avg, s.crit_count);
         }
     }
     // ---------------- observation summary (what sparc_observe computes from the stored state) ----
     if (a.obs) {
-        float m = lane_max<H>(T, lf, spoolf);   // cell 0 is spoolf
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(FULL, m, o));
+        float m = __uint_as_float(__reduce_max_sync(FULL, __float_as_uint(lane_max<H>(T, lf, spoolf))));   // cell 0 is spoolf
         if constexpr (W > 1) {
             __syncthreads();
             if (lane == 0) sm_red[ctx.wid] = (double)m;
