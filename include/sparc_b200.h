@@ -279,6 +279,14 @@ int sparc_step_host_static(void *state, const SparcParams *p, const SparcActions
  * >= 4 MiB of device memory. */
 int sparc_measure_fp32_peak(void *scratch_dev, size_t scratch_bytes, double *tflops_out);
 
+/* Where every wire cell lives in the registers of an environment's lanes (for tests and diagnostics; pure host code).
+ * Each lane holds two "halves" of K/2 slots; half h = 2*lane + {0,1}.  hdr = {K cells per lane, W warps per env,
+ * aligned (1: per-half convection coefficients, 0: per-cell), halves in use}; for every half h < 64*W:
+ * first cell, number of real cells (K/2, K/2-1 with one pad, or 0 when empty) and region (0 below the flushing
+ * zone, 1 zone, 2 above, -1 empty; WireModule gives the zone its own convection coefficient, wire.py:349-374). */
+int sparc_layout_info(const SparcParams *p, int32_t hdr[4], int32_t *half_first, int32_t *half_cells,
+                      int32_t *half_region, int max_halves);
+
 /* Kernel launch geometry chosen for (n_envs, n_segments): lanes per env, slots per lane,
  * threads per block, blocks.  For reporting / tests. */
 int sparc_launch_info(int n_envs, int n_segments, int32_t out[4]);

@@ -44,7 +44,7 @@ EXPORTS = ("sparc_abi_version", "sparc_last_error", "sparc_num_fields", "sparc_f
            "sparc_state_bytes", "sparc_padded_segments", "sparc_init", "sparc_reset", "sparc_reseed", "sparc_reset_reference",
            "sparc_params_bytes", "sparc_step",
            "sparc_step_injected", "sparc_step_ex", "sparc_step_logged", "sparc_step_sampled", "sparc_step_observe", "sparc_observe", "sparc_reduce_stats", "sparc_host_scratch_bytes",
-           "sparc_step_host", "sparc_step_host_static", "sparc_static_max_envs", "sparc_host_action_pitch", "sparc_launch_info", "sparc_measure_fp32_peak")
+           "sparc_step_host", "sparc_step_host_static", "sparc_static_max_envs", "sparc_host_action_pitch", "sparc_launch_info", "sparc_layout_info", "sparc_measure_fp32_peak")
 
 
 def lib():
@@ -87,6 +87,7 @@ def lib():
     L.sparc_step_host_static.argtypes = [vp, PP, PA, i32, i32, u64, u32, vp, vp]
     L.sparc_static_max_envs.restype = i32
     L.sparc_measure_fp32_peak.argtypes = [vp, sz, C.POINTER(C.c_double)]
+    L.sparc_layout_info.argtypes = [PP, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), i32]
     L.sparc_launch_info.argtypes = [i32, i32, C.POINTER(C.c_int32)]
     # a stale or foreign library (SPARC_LIB_PATH) must not be fed a SparcParams of another layout
     if L.sparc_abi_version() != ABI_VERSION or L.sparc_params_bytes() != C.sizeof(SparcParams):

@@ -348,7 +348,7 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
     }
     sparc::SparcLayout lay;
     const Variant *v = pick_variant(p, &lay);
-    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6145 wire segments)");
+    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6657 wire segments)");
     SparcStatePtrs S = make_ptrs(state, n_envs, p->n_segments);
     const sparc::StepFn fn = v->fn[(tlog || signals) ? 1 : 0][draws ? 1 : 0][lay.aligned ? 1 : 0];
     int blocks, threads;
@@ -383,7 +383,10 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
         a.mech_seq = prepass ? next_mech_seq() : 0u;
         a.lay = lay;
         if (ctrl) a.ctrl = *ctrl; else { a.ctrl.kind = 0; a.ctrl.reserved = 0; a.ctrl.desired_gap = a.ctrl.gain = a.ctrl.limit = 0.0; }
-        if (prepass) sparc::mech_launch(*p, S, a, (cudaStream_t)stream);
+        if (prepass) {
+            sparc::mech_launch(*p, S, a, (cudaStream_t)stream);
+            CUDA_TRY(cudaGetLastError());         // never launch the consumer behind a producer that did not start
+        }
         {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3((unsigned)blocks);
@@ -728,6 +731,25 @@ int sparc_measure_fp32_peak(void *scratch_dev, size_t scratch_bytes, double *tfl
     return SPARC_OK;
 }
 
+int sparc_layout_info(const SparcParams *p, int32_t hdr[4], int32_t *half_first, int32_t *half_cells,
+                      int32_t *half_region, int max_halves)
+{
+    if (!p || !hdr || !half_first || !half_cells || !half_region) return fail(SPARC_E_INVALID, "null layout_info argument");
+    if (p->n_segments < 2) return fail(SPARC_E_UNSUPPORTED, "n_segments < 2 is not supported");
+    sparc::SparcLayout L;
+    const Variant *v = pick_variant(p, &L);
+    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6657 wire segments)");
+    const int nh = 64 * v->W;
+    if (max_halves < nh) return fail(SPARC_E_INVALID, "half arrays too small (need 64 * warps per env)");
+    hdr[0] = v->K; hdr[1] = v->W; hdr[2] = L.aligned; hdr[3] = L.hb[3];
+    for (int h = 0; h < nh; h++) {
+        int c0, n, r;
+        sparc::half_geom(L, h, v->K / 2, c0, n, r);
+        half_first[h] = c0; half_cells[h] = n; half_region[h] = r;
+    }
+    return SPARC_OK;
+}
+
 int sparc_launch_info(int n_envs, int n_segments, int32_t out[4])
 {
     if (!out || n_envs <= 0 || n_segments < 2) return fail(SPARC_E_INVALID, "bad launch_info arguments");
@@ -735,7 +757,7 @@ int sparc_launch_info(int n_envs, int n_segments, int32_t out[4])
     memset(&q, 0, sizeof(q));                    // except through K when the aligned layout needs more slack)
     q.n_segments = n_segments;
     const Variant *v = pick_variant(&q, nullptr);
-    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6145 wire segments)");
+    if (!v) return fail(SPARC_E_UNSUPPORTED, "n_segments too large (max 6657 wire segments)");
     int blocks, threads;
     launch_geometry(v, n_envs, &blocks, &threads);
     out[0] = 32 * v->W;

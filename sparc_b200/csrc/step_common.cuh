@@ -116,6 +116,27 @@ struct StepArgs {
     SparcController ctrl;    // kind 0: the servo command is act.servo[e]
 };
 
+// First cell, number of real cells (H, H-1 or 0) and region of half h under layout L (host + device: the host
+// exposes it through sparc_layout_info for the CPU-side layout sweep in tests/test_abi_cpu.py).
+__host__ __device__ __forceinline__ void half_geom(const SparcLayout &L, const int h, const int H, int &c_first, int &n, int &region)
+{
+    if (h >= L.hb[3]) { c_first = 0; n = 0; region = -1; return; }
+    const int r = (h >= L.hb[2]) ? 2 : ((h >= L.hb[1]) ? 1 : 0);
+    const int k = h - L.hb[r], p = L.p[r];
+    int before, sh;
+    if (L.aligned) {                            // pads only in y halves: the first p odd halves of the region
+        const int cnt = (L.hb[r] & 1) ? ((k + 1) >> 1) : (k >> 1);      // odd halves of the region before h
+        before = (cnt < p) ? cnt : p;
+        sh = ((h & 1) && cnt < p) ? 1 : 0;
+    } else {                                    // the first p halves of the (single) region
+        before = (k < p) ? k : p;
+        sh = (k < p) ? 1 : 0;
+    }
+    c_first = L.cb[r] + k * H - before;
+    n = H - sh;
+    region = r;
+}
+
 // The servo command of this launch: the staged action, or the in-kernel controller evaluated from the
 // state the launch starts with (SparcController, include/sparc_b200.h).  mech_kernel and step_kernel
 // both call it at their start and read the same stored state (the step kernel overwrites wp / wire

@@ -53,25 +53,6 @@ struct LaneGeom {
     int rx, ry;             // region of each half (-1: empty)
 };
 
-__device__ __forceinline__ void half_geom(const SparcLayout &L, const int h, const int H, int &c_first, int &n, int &region)
-{
-    if (h >= L.hb[3]) { c_first = 0; n = 0; region = -1; return; }
-    const int r = (h >= L.hb[2]) ? 2 : ((h >= L.hb[1]) ? 1 : 0);
-    const int k = h - L.hb[r], p = L.p[r];
-    int before, sh;
-    if (L.aligned) {                            // pads only in y halves: the first p odd halves of the region
-        const int cnt = (L.hb[r] & 1) ? ((k + 1) >> 1) : (k >> 1);      // odd halves of the region before h
-        before = (cnt < p) ? cnt : p;
-        sh = ((h & 1) && cnt < p) ? 1 : 0;
-    } else {                                    // the first p halves of the (single) region
-        before = (k < p) ? k : p;
-        sh = (k < p) ? 1 : 0;
-    }
-    c_first = L.cb[r] + k * H - before;
-    n = H - sh;
-    region = r;
-}
-
 __device__ __forceinline__ LaneGeom lane_geom(const SparcLayout &L, const int gl, const int H)
 {
     LaneGeom g;

@@ -162,3 +162,48 @@ def test_prepass_handoff_is_in_the_machine_code(native):
     step = sass("step_inst_w1.o")
     poll = step[step.index("mech_wait"):] if "mech_wait" in step else step
     assert re.search(r"LDG\.E\.STRONG\.GPU", poll) and "CCTL.IVALL" in poll
+
+
+def test_region_layout_covers_every_cell_exactly_once(native):
+    """The register layout of the wire (SparcLayout): for a sweep of geometries — every segment count the reference's
+    expressions can produce in 2..6657 on a coarse grid, zones at the start, the end, empty, covering everything —
+    the halves must hold cells 1..N-1 exactly once and in order, pads only where the stencil expects them (aligned
+    layouts: y halves only), every half inside one convection region, the wire ending on the last half in use."""
+    from sparc_b200.params import SparcParams
+
+    L = native.lib()
+    rng = np.random.default_rng(7)
+    geoms = [(375, 149, 223), (400, 149, 248), (550, 149, 398), (1100, 299, 798), (2200, 599, 1598), (5500, 1499, 3998)]
+    for n in list(range(2, 80)) + [int(x) for x in rng.integers(80, 6657, 400)] + [769, 770, 1152, 1153, 2304, 2305, 6656, 6657]:
+        za = int(rng.integers(0, n + 1))
+        zb = int(rng.integers(za, n + 1))
+        geoms += [(n, za, zb), (n, 0, n), (n, n, n), (n, 1, 1), (n, 0, 0), (n, n // 3, 2 * n // 3)]
+    hf, hc, hr = (C.c_int32 * 512)(), (C.c_int32 * 512)(), (C.c_int32 * 512)()
+    hdr = (C.c_int32 * 4)()
+    n_aligned = 0
+    for n, za, zb in geoms:
+        p = SparcParams()
+        p.n_segments, p.actual_zone_start, p.actual_zone_end = n, min(za, n - 1), zb
+        rc = L.sparc_layout_info(C.byref(p), hdr, hf, hc, hr, 512)
+        assert rc == 0, (n, za, zb, L.sparc_last_error())
+        K, W, aligned, used = list(hdr)
+        H = K // 2
+        assert K % 2 == 0 and K * 32 * W >= n - 1 and used <= 64 * W
+        n_aligned += aligned
+        cells, nxt = 0, 1
+        for h in range(64 * W):
+            first, cnt, reg = hf[h], hc[h], hr[h]
+            if h >= used:
+                assert cnt == 0 and reg == -1
+                continue
+            assert cnt in (H, H - 1) and first == nxt, (n, za, zb, h, first, nxt)
+            if aligned:
+                assert cnt == H or h % 2 == 1, "aligned layouts keep pads in y halves"
+                inside = [p.actual_zone_start <= c < p.actual_zone_end for c in range(first, first + cnt)]
+                assert all(inside) or not any(inside), (n, za, zb, h, "a half straddles the zone boundary")
+            nxt += cnt
+            cells += cnt
+        assert cells == n - 1 and nxt == n, (n, za, zb, cells)
+        if aligned:
+            assert used % 2 == 0, "the wire ends on a y half"
+    assert n_aligned > len(geoms) // 2
