@@ -143,3 +143,61 @@ def oracle_overrides(case: dict) -> dict:
         for k, v in case.get(grp, {}).items():
             ov[k] = int(v) if isinstance(v, bool) else v
     return ov
+
+
+# ------------------------------------------------------------------------------------------------
+# Geometry sweep: the register layout of the wire depends on (n_segments, zone, contacts); these
+# cases move every one of them — tiny wires, zones that touch either end, contacts clipped to
+# the wire, buffers shorter than the contact offsets, segment counts on both sides of every
+# cells-per-lane / warps-per-env boundary.  Each runs 3000 µs with a few forced sparks.
+# Reference geometry expressions: wire.py:143-156, 208-252.
+# ------------------------------------------------------------------------------------------------
+def _geometry_case(h, seg, bb, bt, ob, ot, key, dia=0.25, zone_mean=False, action=None, gap=30.0):
+    n_us = 3000
+    forced = tuple(int(t) for t in np.random.default_rng(key).choice(np.arange(20, n_us - 300), 7, replace=False))
+    wire = dict(segment_len=seg, buffer_len_bottom=bb, buffer_len_top=bt, contact_offset_bottom=ob,
+                contact_offset_top=ot)
+    if zone_mean:
+        wire.update(compute_zone_mean=True, zone_mean_interval=64)
+    return dict(config=dict(workpiece_height=h, wire_diameter=dia, target_cutting_distance=800.0, initial_gap=gap),
+                mode="position", wire=wire, actions=[action or [0.02, 90.0, 11, 2.5, 25.0]],
+                tape=("philox_forced", (key, forced)), n_us=n_us)
+
+
+def geometry_cases() -> dict:
+    out = {
+        # N = 5: four cells in one lane, zone of two segments
+        "geo_tiny": _geometry_case(0.4, 0.2, 0.3, 0.3, 0.2, 0.2, 901),
+        # N = 33..34: one cell per lane and a remainder
+        "geo_lanes_plus_one": _geometry_case(3.0, 0.2, 1.9, 1.9, 1.0, 1.0, 902, zone_mean=True),
+        # zone starts at segment 0 (no bottom buffer), contact offset longer than the buffer
+        "geo_zone_at_start": _geometry_case(12.0, 0.2, 0.0, 25.0, 10.0, 5.0, 903),
+        # zone runs to the last segment (no top buffer)
+        "geo_zone_at_end": _geometry_case(18.0, 0.25, 22.0, 0.0, 6.0, 10.0, 904, dia=0.2),
+        # the workpiece covers the whole wire
+        "geo_all_zone": _geometry_case(30.0, 0.1, 0.0, 0.0, 10.0, 10.0, 905, zone_mean=True),
+        # workpiece thinner than one segment: empty zone in index terms
+        "geo_thin_plate": _geometry_case(0.15, 0.2, 20.0, 31.0, 10.0, 10.0, 906),
+        # N = 769 / 1153 / 2305: first sizes past one, two and four warps per env
+        "geo_769": _geometry_case(36.9, 0.1, 20.0, 20.0, 10.0, 10.0, 907),
+        "geo_1153": _geometry_case(55.3, 0.1, 30.0, 30.0, 12.0, 3.0, 908, dia=0.3),
+        "geo_2305": _geometry_case(45.25, 0.05, 35.0, 35.0, 10.0, 40.0, 909),
+        # asymmetric buffers, odd segment length (floor vs divide differ), thin wire
+        "geo_odd_pitch": _geometry_case(17.3, 0.07, 11.0, 43.0, 3.3, 17.0, 910, dia=0.1, zone_mean=True,
+                                        action=[0.0, 70.0, 7, 1.5, 15.0]),
+        # N = 6650: near the largest supported size, short zone in the middle
+        "geo_max": _geometry_case(13.0, 0.02, 60.0, 60.0, 10.0, 10.0, 911),
+    }
+    g = np.random.default_rng(20260207)
+    for k in range(6):
+        seg = float(np.round(g.choice([0.03, 0.05, 0.08, 0.13, 0.2, 0.37, 0.5]), 3))
+        h = float(np.round(g.uniform(0.5, 60.0), 2))
+        bb, bt = (float(np.round(x, 2)) for x in g.uniform(0.0, 40.0, 2))
+        ob, ot = (float(np.round(x, 2)) for x in g.uniform(0.0, 20.0, 2))
+        out[f"geo_random_{k}"] = _geometry_case(h, seg, bb, bt, ob, ot, 920 + k, dia=float(g.choice([0.15, 0.2, 0.25])),
+                                                zone_mean=bool(k % 2))
+    return out
+
+
+GEOMETRY_CASES = geometry_cases()
+ALL_CASES = {**CASES, **GEOMETRY_CASES}

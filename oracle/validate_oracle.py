@@ -1,6 +1,6 @@
 """Pin the C oracle against the RUNNING reference (build container only).
 
-TEST INFRASTRUCTURE ONLY.  For every case in oracle/cases.py: run the unmodified reference
+TEST INFRASTRUCTURE ONLY.  For every case in oracle/cases.py (CASES and the GEOMETRY_CASES sweep): run the unmodified reference
 with the injected tape, run `oracle/wedm_oracle.c` on the same tape and recorded actions,
 compare every per-µs field.  With `--write-golden` the reference trajectories are written
 to tests/golden/<case>.npz (the committed fixtures; this script is their generator).
@@ -46,7 +46,7 @@ def reference_controller(case):
 
 
 def run_case_reference(name, per_us=True):
-    case = CS.CASES[name]
+    case = CS.ALL_CASES[name]
     env = RR.make_env(case.get("config"), case.get("mode", "position"),
                       ignition=case.get("ignition"), wire=case.get("wire"),
                       material=case.get("material"), dielectric=case.get("dielectric"),
@@ -156,7 +156,7 @@ def main():
     ap.add_argument("cases", nargs="*")
     ap.add_argument("--write-golden", action="store_true")
     args = ap.parse_args()
-    names = [c for c in args.cases if c != "reference_reset"] or ([] if args.cases else list(CS.CASES))
+    names = [c for c in args.cases if c != "reference_reset"] or ([] if args.cases else list(CS.ALL_CASES))
     all_ok = True
     for name in names:
         case, tape, ref = run_case_reference(name)
@@ -175,7 +175,8 @@ def main():
             # keep fixtures small: per-µs ints (compress well) + per-µs f64 for the first
             # 3000 µs, then every 50th µs; T snapshots every 1000 µs.
             n = len(ref["f64"])
-            keep = np.unique(np.concatenate([np.arange(min(n, 3000)), np.arange(0, n, 50), [n - 1]]))
+            dense = 0 if name in CS.GEOMETRY_CASES else min(n, 3000)      # geometry sweep: every 50th µs only
+            keep = np.unique(np.concatenate([np.arange(dense), np.arange(49, n, 50), np.arange(0, n, 50), [n - 1]]))
             np.savez_compressed(
                 os.path.join(GOLDEN_DIR, f"{name}.npz"),
                 f64=ref["f64"][keep], f64_rows=keep, i32=ref["i32"].astype(np.int32),

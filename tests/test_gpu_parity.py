@@ -20,14 +20,14 @@ def _golden(name):
     return np.load(os.path.join(GOLDEN_DIR, f"{name}.npz"))
 
 
-@pytest.mark.parametrize("name", sorted(CS.CASES))
+@pytest.mark.parametrize("name", sorted(CS.ALL_CASES))
 def test_trajectory_matches_reference_golden(name):
     """µs-by-µs (1-µs launches) for the first 3000 µs, then at every 50th µs, against the
     fixtures generated from the unmodified reference."""
     import torch
 
     g = _golden(name)
-    case = CS.CASES[name]
+    case = CS.ALL_CASES[name]
     tape = CS.case_tape(case)
     actions = g["actions"]
     eng = PU.make_engine(case, n_envs=3)
@@ -53,14 +53,14 @@ def test_trajectory_matches_reference_golden(name):
     print(f"\n[{name}] {n_done} µs matched; max |tmax_gpu - tmax_ref| = {max_t_err:.3e} K")
 
 
-@pytest.mark.parametrize("name", sorted(CS.CASES))
+@pytest.mark.parametrize("name", sorted(CS.ALL_CASES))
 def test_control_step_launches_match_oracle(name):
     """1000-µs launches (the production path) against the oracle: every scalar and the whole
     temperature field at each control-step boundary."""
     import torch
 
     g = _golden(name)
-    case = CS.CASES[name]
+    case = CS.ALL_CASES[name]
     actions = g["actions"]
     orc_env, tape, orc = PU.run_oracle_case(case, actions, rec_every=1000, t_every=1000)
     eng = PU.make_engine(case, n_envs=5)
@@ -177,7 +177,7 @@ def test_logged_temperature_field_matches_oracle(name, log_every):
     import torch
 
     g = _golden(name)
-    case = CS.CASES[name]
+    case = CS.ALL_CASES[name]
     actions = g["actions"]
     n_us = min(case["n_us"], 4000) if name != "hot_break" else case["n_us"]
     orc_env, tape, orc = PU.run_oracle_case(dict(case, n_us=n_us), actions, rec_every=1000, t_every=log_every)
@@ -246,7 +246,7 @@ def test_signal_log_matches_reference_golden(name):
     from sparc_b200 import _native as N
 
     g = _golden(name)
-    case = CS.CASES[name]
+    case = CS.ALL_CASES[name]
     tape = CS.case_tape(case)
     actions = g["actions"]
     rows = g["f64_rows"]

@@ -18,10 +18,10 @@ def _load(name):
     return np.load(os.path.join(GOLDEN_DIR, f"{name}.npz"))
 
 
-@pytest.mark.parametrize("name", sorted(CS.CASES))
+@pytest.mark.parametrize("name", sorted(CS.ALL_CASES))
 def test_oracle_matches_reference_golden(name):
     g = _load(name)
-    case = CS.CASES[name]
+    case = CS.ALL_CASES[name]
     tape = CS.case_tape(case)
     e = O.OracleEnv(**CS.oracle_overrides(case))
     if "unwind_v" in case:
