@@ -398,6 +398,13 @@ int launch_step(void *state, const SparcParams *p, const SparcActions *actions, 
                 dyn = (size_t)SPARC_LOG_NBUF(v->W) * n_stage * sizeof(float) * (v->W == 1 ? SPARC_BLOCK_THREADS / 32 : 1);
                 if (dyn > 40 * 1024) CUDA_TRY(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
             }
+#ifdef SPARC_EXPERIMENT_KNOBS   /* experiments only: cap the resident blocks per SM with unused dynamic shared memory */
+            static const char *exp_dyn = getenv("SPARC_EXP_DYNSMEM");
+            if (exp_dyn && dyn == 0) {
+                dyn = (size_t)atoi(exp_dyn);
+                if (dyn > 40 * 1024) CUDA_TRY(cudaFuncSetAttribute((const void *)fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+            }
+#endif
             cfg.dynamicSmemBytes = dyn;
             cfg.stream = (cudaStream_t)stream;
             cudaLaunchAttribute attr[1];

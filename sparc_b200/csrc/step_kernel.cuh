@@ -17,9 +17,13 @@
 //     slots used to be per-cell coefficient registers (cE, c0, cR per cell).  Now the cells are laid out
 //     so that every such boundary falls between two HALVES of a lane: the conduction coefficient is one
 //     scalar for the whole wire, the convection pair one value per half, the zero-flux end is a halo
-//     override, and pads sit in compile-time slots that mirror their right-hand neighbour.  Element by
-//     element the operation sequence on real cells is unchanged (q = fma(cE,T,c0); q = fma(cR,dnext,q);
-//     q = fma(ncL,dprev,q); T += q), so the field is bit-identical to round 1's.
+//     override, and pads sit in compile-time slots that mirror their right-hand neighbour.
+//   * FOUR packed FP32 instructions per pair of cells and µs: q = fma(cC,T,c0); q = fma(cR,T_next,q);
+//     q = fma(cL,T_prev,q); T += q, with cC = cE - (cR + cL) (stencil_apply).  The form with explicit
+//     differences (five packed instructions and three scalar subtractions per lane and µs) was the kernel's
+//     FMA-pipe bound; the coefficients are rounded so that cC + cR + cL is exactly the convection weight
+//     (see "stencil coefficients" below), which keeps the per-µs error of q near 5e-8 K, two to three
+//     orders of magnitude under the fp32 rounding of T' = T + q that the reference performs as well.
 //   * Philox ignition words are computed for 128 µs at a time (each lane one counter, all four
 //     words kept) instead of 32.
 //
@@ -110,11 +114,15 @@ __device__ __forceinline__ void stencil_edges(EnvCtx<W> &c, float2 (&T)[H], cons
     }
 }
 
-// Convection coefficients: one (cE, c0) pair per half when the layout is aligned, per cell otherwise.
+// Per-cell coefficients of the update T' = T + q, q = cC*T + c0 + cR*T_next + cL*T_prev, where
+//   cC = cE - (cR + cL), cE = -f*h*A (convection, wire.py:108-111), c0 = -cE*T_dielectric,
+//   cR = f*k_cond (wire.py:66-75), cL = f*(k_cond + adv) (advection folded in, wire.py:113-119).
+// One (cC, c0) pair per half when the layout is aligned, per cell otherwise.  See stencil_coefficients()
+// for how the four numbers are rounded so that a uniform field is a fixed point of the conduction part.
 template <int H, bool ALIGNED>
 struct Coefs {
-    float2 cE[ALIGNED ? 1 : H], c0[ALIGNED ? 1 : H];
-    __device__ __forceinline__ float2 e(const int j) const { return cE[ALIGNED ? 0 : j]; }
+    float2 cC[ALIGNED ? 1 : H], c0[ALIGNED ? 1 : H];
+    __device__ __forceinline__ float2 e(const int j) const { return cC[ALIGNED ? 0 : j]; }
     __device__ __forceinline__ float2 z(const int j) const { return c0[ALIGNED ? 0 : j]; }
 };
 
@@ -132,51 +140,80 @@ __device__ __forceinline__ float lane_max(const float2 (&T)[H], const LaneFlags 
     return fmaxf(mx, my);
 }
 
-// One µs of compute_thermal_update (wire.py:58-123) without heat sources: the halo-independent pairs
-// first so the shuffles complete underneath them (measured +2 % in round 1).
-template <int H, bool ALIGNED, int W>
+// Conduction + advection of one µs on top of acc[j] (= the convection term + sources), then T += q.  The SAME
+// function and the same order of accumulation serve quiet and general µs, so a cell's value does not depend
+// on which path executed a µs.  Two forms, chosen per env from its conduction weights (DIFF, see "stencil
+// coefficients" in step_env):
+//   DIFF = false  q = fma(cR, T_next, acc); q = fma(cL, T_prev, q) with acc = fma(cC, T, c0), cC = cE - (cR + cL):
+//                 FOUR packed FP32 instructions per pair of cells and µs.  The products are of magnitude
+//                 (cR + cL)*T, so q carries a rounding error of ~ulp((cR + cL)*T): used when cR + cL <= 2^-6,
+//                 where that is <= 1/64 of the rounding T' = T + q performs anyway (README default: 2^-9).
+//   DIFF = true   q = fma(cR, T_next - T, acc); q = fma(-cL, T - T_prev, q) with acc = fma(cE, T, c0): five
+//                 packed instructions and three scalar subtractions per lane; exact differences, for fine
+//                 segmentations (cR + cL up to 0.5), and the round-1 arithmetic bit for bit.
+// The halo-independent terms come first so that the shuffles complete underneath them.
+template <int H, bool DIFF>
+__device__ __forceinline__ void stencil_apply(float2 (&T)[H], float2 (&acc)[H], const float2 cR2, const float2 cL2,
+                                              const float left, const float right, const float xl, const float yv)
+{
+    if constexpr (!DIFF) {
+#pragma unroll
+        for (int j = 0; j < H - 1; j++) acc[j] = __ffma2_rn(cR2, T[j + 1], acc[j]);
+#pragma unroll
+        for (int j = 1; j < H; j++) acc[j] = __ffma2_rn(cL2, T[j - 1], acc[j]);
+        acc[H - 1] = __ffma2_rn(cR2, make_float2(yv, right), acc[H - 1]);
+        acc[0] = __ffma2_rn(cL2, make_float2(left, xl), acc[0]);
+#pragma unroll
+        for (int j = 0; j < H; j++) T[j] = __fadd2_rn(T[j], acc[j]);
+    } else {                                    // cL2 holds -cL here
+        const float d_mid = yv - xl;
+        const float2 d0 = sub2(T[1], T[0]);     // dnext of pair 0, dprev of pair 1 (old values)
+        float2 dprev = d0;
+#pragma unroll
+        for (int j = 1; j < H - 1; j++) {
+            const float2 dnext = sub2(T[j + 1], T[j]);
+            float2 q = __ffma2_rn(cR2, dnext, acc[j]);
+            q = __ffma2_rn(cL2, dprev, q);
+            dprev = dnext;
+            T[j] = __fadd2_rn(T[j], q);
+        }
+        {
+            const float2 dlast = make_float2(d_mid, right - T[H - 1].y);
+            float2 q = __ffma2_rn(cR2, dlast, acc[H - 1]);
+            q = __ffma2_rn(cL2, dprev, q);
+            T[H - 1] = __fadd2_rn(T[H - 1], q);
+        }
+        {
+            const float2 dfirst = make_float2(T[0].x - left, d_mid);
+            float2 q = __ffma2_rn(cR2, d0, acc[0]);
+            q = __ffma2_rn(cL2, dfirst, q);
+            T[0] = __fadd2_rn(T[0], q);
+        }
+    }
+}
+
+// One µs of compute_thermal_update (wire.py:58-123) without heat sources.
+template <int H, bool ALIGNED, int W, bool DIFF>
 __device__ __forceinline__ void stencil_quiet_us(float2 (&T)[H], const Coefs<H, ALIGNED> &co, const float2 cR2,
-                                                 const float2 ncL2, const float spoolf, const LaneFlags &f, EnvCtx<W> &ctx)
+                                                 const float2 cL2, const float spoolf, const LaneFlags &f, EnvCtx<W> &ctx)
 {
     float left, right, xl, yv;
     stencil_edges<H, W, !ALIGNED>(ctx, T, f, spoolf, left, right, xl, yv);
-    const float d_mid = yv - xl;
-    const float2 d0 = sub2(T[1], T[0]);         // dnext of pair 0, dprev of pair 1 (old values)
-    float2 dprev = d0;
+    float2 acc[H];
 #pragma unroll
-    for (int j = 1; j < H - 1; j++) {
-        const float2 dnext = sub2(T[j + 1], T[j]);
-        float2 q = __ffma2_rn(co.e(j), T[j], co.z(j));
-        q = __ffma2_rn(cR2, dnext, q);
-        q = __ffma2_rn(ncL2, dprev, q);
-        dprev = dnext;
-        T[j] = __fadd2_rn(T[j], q);
-    }
-    {
-        const float2 dlast = make_float2(d_mid, right - T[H - 1].y);
-        float2 q = __ffma2_rn(co.e(H - 1), T[H - 1], co.z(H - 1));
-        q = __ffma2_rn(cR2, dlast, q);
-        q = __ffma2_rn(ncL2, dprev, q);
-        T[H - 1] = __fadd2_rn(T[H - 1], q);
-    }
-    {
-        const float2 dfirst = make_float2(T[0].x - left, d_mid);
-        float2 q = __ffma2_rn(co.e(0), T[0], co.z(0));
-        q = __ffma2_rn(cR2, d0, q);
-        q = __ffma2_rn(ncL2, dfirst, q);
-        T[0] = __fadd2_rn(T[0], q);
-    }
+    for (int j = 0; j < H; j++) acc[j] = __ffma2_rn(co.e(j), T[j], co.z(j));
+    stencil_apply<H, DIFF>(T, acc, cR2, cL2, left, right, xl, yv);
 }
 
 // n quiet µs.  HOT additionally runs _check_wire_breaking (wire.py:376-388) every µs and returns the
 // number of µs executed (n, or k+1 when the wire broke on µs k; `broke` says which).
-template <int H, bool HOT, bool ALIGNED, int W, bool LOG, class LogTick, class SigCap>
-__device__ __forceinline__ int run_quiet(float2 (&T)[H], const Coefs<H, ALIGNED> &co, const float cRf, const float ncL,
+template <int H, bool HOT, bool ALIGNED, int W, bool LOG, bool DIFF, class LogTick, class SigCap>
+__device__ __forceinline__ int run_quiet_t(float2 (&T)[H], const Coefs<H, ALIGNED> &co, const float cRf, const float cLf,
                                          const float spoolf, const LaneFlags &f, EnvCtx<W> &ctx, const int n,
                                          const float crit_T, const float break_T, int &crit_count, bool &broke,
                                          bool &cold_after, LogTick &&log_tick, SigCap &&sig_cap)
 {
-    const float2 ncL2 = make_float2(ncL, ncL), cR2 = make_float2(cRf, cRf);
+    const float2 cL2 = make_float2(cLf, cLf), cR2 = make_float2(cRf, cRf);
     const float gate_T = fminf(crit_T, break_T);
     broke = false;
 #ifdef SPARC_ABL_NOSTENCIL
@@ -186,16 +223,16 @@ __device__ __forceinline__ int run_quiet(float2 (&T)[H], const Coefs<H, ALIGNED>
         int k = 0;
 #pragma unroll 1
         for (; k + 2 <= n; k += 2) {
-            stencil_quiet_us<H, ALIGNED, W>(T, co, cR2, ncL2, spoolf, f, ctx);
-            stencil_quiet_us<H, ALIGNED, W>(T, co, cR2, ncL2, spoolf, f, ctx);
+            stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
+            stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
         }
-        if (k < n) stencil_quiet_us<H, ALIGNED, W>(T, co, cR2, ncL2, spoolf, f, ctx);
+        if (k < n) stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
         crit_count = 0;
         return n;
     }
 #pragma unroll 1
     for (int k = 0; k < n; k++) {
-        stencil_quiet_us<H, ALIGNED, W>(T, co, cR2, ncL2, spoolf, f, ctx);
+        stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
         if (LOG) log_tick();
         if (HOT) {
             const float lmax = lane_max<H>(T, f, spoolf);
@@ -212,6 +249,20 @@ __device__ __forceinline__ int run_quiet(float2 (&T)[H], const Coefs<H, ALIGNED>
     }
     if (!HOT) crit_count = 0;
     return n;
+}
+
+// run_quiet_t in the form this env's stencil uses (`diff`, uniform over the env's warps)
+template <int H, bool HOT, bool ALIGNED, int W, bool LOG, class LogTick, class SigCap>
+__device__ __forceinline__ int run_quiet(const bool diff, float2 (&T)[H], const Coefs<H, ALIGNED> &co, const float cRf,
+                                         const float cLf, const float spoolf, const LaneFlags &f, EnvCtx<W> &ctx, const int n,
+                                         const float crit_T, const float break_T, int &crit_count, bool &broke,
+                                         bool &cold_after, LogTick &log_tick, SigCap &sig_cap)
+{
+    if (diff)
+        return run_quiet_t<H, HOT, ALIGNED, W, LOG, true>(T, co, cRf, cLf, spoolf, f, ctx, n, crit_T, break_T, crit_count, broke,
+                                                          cold_after, log_tick, sig_cap);
+    return run_quiet_t<H, HOT, ALIGNED, W, LOG, false>(T, co, cRf, cLf, spoolf, f, ctx, n, crit_T, break_T, crit_count, broke,
+                                                       cold_after, log_tick, sig_cap);
 }
 
 // resident blocks per SM the register budget is sized for (64-thread blocks: 8 -> 16 warps/SM).  Measured in
@@ -417,41 +468,61 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
     }
 
     // ---------------- stencil coefficients ---------------------------------------------------
+    // (forms: stencil_apply.)  Four-instruction form: q = cC*T + c0 + cR*T_next + cL*T_prev, cC = cE - (cR + cL).
+    // The three conduction weights must cancel EXACTLY on a uniform field, otherwise every µs adds
+    // (cC + cR + cL - cE)*T ~ 1e-10 * T of the same sign to every cell.  So: csum = fl(cR + cL); the smaller of
+    // the two weights is replaced by csum - larger (exact in fp32; a relative change of <= 2^-24 * larger/smaller
+    // of one conduction weight); cC = fl(cE - csum), and the convection weight the update really applies,
+    // cC + csum (exact; differs from cE by <= ulp(csum)/2, ~1e-6 of cE), is the one that c0 = -(cC + csum)*T_diel
+    // is formed with, in fp64.  Difference form (fine segmentations, csum > 2^-6): the plain weights.
     const double f = P.temp_update_factor;
-    float cRf, ncL;
+    float cRf, cLf, csum;
+    bool diff_form;
     {
         const double unwind_v = S.unwind_v[e];
         double adv = 0.0;                       // wire.py:299-309
         if (fabs(unwind_v) > 1e-6) adv = P.density_times_cp * fabs(unwind_v) * P.S;
         if (!(fabs(adv) > 1e-9)) adv = 0.0;     // wire.py:114
         cRf = P.cond_coeff_f32;                  // (float)(f * k_cond_coeff), rounded on the host
-        ncL = -(float)(f * (P.k_cond_coeff + adv));
+        cLf = (float)(f * (P.k_cond_coeff + adv));
+        csum = cRf + cLf;
+        diff_form = !(csum <= 0.015625f);
+#ifdef SPARC_FORCE_DIFF_FORM
+        diff_form = true;
+#endif
+        if (diff_form) cLf = -cLf;              // stencil_apply<DIFF> multiplies T - T_prev
+        else if (fabsf(cLf) >= fabsf(cRf)) cRf = csum - cLf;
+        else cLf = csum - cRf;
     }
     const float gate_T = fminf(P.critical_temperature_f32, P.breaking_temperature_f32);
     Coefs<H, ALIGNED> co;
     auto conv_pair = [&](float h, float &e_, float &z_) {
         const double hA = (double)h * P.A;      // conv_coeff, wire.py:110
-        e_ = (float)(-(f * hA));
-        z_ = (float)(f * hA * P.dielectric_temperature);
+        if (diff_form) {
+            e_ = (float)(-(f * hA));
+            z_ = (float)(f * hA * P.dielectric_temperature);
+        } else {
+            e_ = (float)(-(f * hA)) - csum;
+            z_ = (float)(-((double)e_ + (double)csum) * P.dielectric_temperature);
+        }
     };
     auto refresh_coeffs = [&](float hb, float he) {
+        // slots that hold no cell (pads, empty halves) get h = 0: pure conduction, bounded
         if constexpr (ALIGNED) {
-            co.cE[0] = make_float2(0.f, 0.f); co.c0[0] = make_float2(0.f, 0.f);
-            if (geom.rx >= 0) conv_pair(geom.rx == 1 ? he : hb, co.cE[0].x, co.c0[0].x);
-            if (geom.ry >= 0) conv_pair(geom.ry == 1 ? he : hb, co.cE[0].y, co.c0[0].y);
+            conv_pair(geom.rx >= 0 ? (geom.rx == 1 ? he : hb) : 0.f, co.cC[0].x, co.c0[0].x);
+            conv_pair(geom.ry >= 0 ? (geom.ry == 1 ? he : hb) : 0.f, co.cC[0].y, co.c0[0].y);
         } else {
 #pragma unroll
             for (int j = 0; j < H; j++) {
-                co.cE[j] = make_float2(0.f, 0.f); co.c0[j] = make_float2(0.f, 0.f);
                 const int ix = geom.cx0 + j, iy = geom.cy0 + j;
-                if (j < geom.nx) conv_pair((ix >= P.actual_zone_start && ix < P.actual_zone_end) ? he : hb, co.cE[j].x, co.c0[j].x);
-                if (j < geom.ny) conv_pair((iy >= P.actual_zone_start && iy < P.actual_zone_end) ? he : hb, co.cE[j].y, co.c0[j].y);
+                conv_pair(j < geom.nx ? ((ix >= P.actual_zone_start && ix < P.actual_zone_end) ? he : hb) : 0.f, co.cC[j].x, co.c0[j].x);
+                conv_pair(j < geom.ny ? ((iy >= P.actual_zone_start && iy < P.actual_zone_end) ? he : hb) : 0.f, co.cC[j].y, co.c0[j].y);
             }
         }
         const float hmax = fmaxf(hb, he), hmin = fminf(hb, he);
         const float ce_max = (float)(f * ((double)hmax * P.A));
         // T' is a convex combination of T and T_diel when no source is on: the maximum cannot grow
-        s.convex = hmin >= 0.0f && cRf >= 0.0f && ncL <= 0.0f && (cRf - ncL + ce_max) <= 0.999f &&
+        s.convex = hmin >= 0.0f && cRf >= 0.0f && csum >= cRf && (csum + ce_max) <= 0.999f &&
                    fmaxf((float)P.dielectric_temperature, spoolf) < gate_T - 1.0f;
     };
     refresh_coeffs(S.h_base[e], S.h_enh[e]);
@@ -631,7 +702,7 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
 #ifdef SPARC_ABL_ALLQUIET
     {   // ablation: the whole launch as ONE cold quiet run (stencil speed inside this kernel)
         bool broke = false, cold_after = true; int cc = 0;
-        run_quiet<H, false, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, a.n_us, 0.f, 0.f, cc, broke, cold_after, log_tick, sig_cap);
+        run_quiet<H, false, ALIGNED, W, false>(diff_form, T, co, cRf, cLf, spoolf, lf, ctx, a.n_us, 0.f, 0.f, cc, broke, cold_after, log_tick, sig_cap);
         s.time += a.n_us; it = a.n_us; need_mech(a.n_us);
     }
 #endif
@@ -666,9 +737,6 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                 cur_post = nxt_post;            // requested with index it + lane during the previous block
                 p0 = R.pos[prev_nb];            // wire after the last µs of the previous block
             }
-            int idx = it + nb + lane;
-            if (idx > a.n_us - 1) idx = a.n_us - 1;
-            nxt_post = __ldcg(traj + idx);
             __syncwarp();
             R.pos[lane + 1] = cur_post;
             if (lane == 0) R.pos[0] = p0;
@@ -691,6 +759,14 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
             }
         }
         __syncwarp();
+        {   // next block's positions: requested only now, AFTER this block's were stored.  Issued before that store,
+            // the load took the scoreboard the store of cur_post waits on, and the store then sat out the whole L2
+            // round trip of a load it does not depend on (7.9 % of the kernel's stall samples on that one STS,
+            // profiles/r02b_cfg2_line_profile.txt).
+            int idx = it + nb + lane;
+            if (idx > a.n_us - 1) idx = a.n_us - 1;
+            nxt_post = __ldcg(traj + idx);
+        }
 
         int i = 0;
         while (i < nb) {
@@ -771,17 +847,17 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                 const bool cold = s.cold_ok && s.convex;
                 if (!LOG || !(logging || sig_on)) {
                     if (cold)
-                        nx = run_quiet<H, false, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, n, 0.f, 0.f, crit_count,
+                        nx = run_quiet<H, false, ALIGNED, W, false>(diff_form, T, co, cRf, cLf, spoolf, lf, ctx, n, 0.f, 0.f, crit_count,
                                                                     broke, cold_after, log_tick, sig_cap);
                     else
-                        nx = run_quiet<H, true, ALIGNED, W, false>(T, co, cRf, ncL, spoolf, lf, ctx, n, P.critical_temperature_f32,
+                        nx = run_quiet<H, true, ALIGNED, W, false>(diff_form, T, co, cRf, cLf, spoolf, lf, ctx, n, P.critical_temperature_f32,
                                                                    P.breaking_temperature_f32, crit_count, broke, cold_after, log_tick, sig_cap);
                 } else {
                     if (cold)
-                        nx = run_quiet<H, false, ALIGNED, W, LOG>(T, co, cRf, ncL, spoolf, lf, ctx, n, 0.f, 0.f, crit_count, broke,
+                        nx = run_quiet<H, false, ALIGNED, W, LOG>(diff_form, T, co, cRf, cLf, spoolf, lf, ctx, n, 0.f, 0.f, crit_count, broke,
                                                                   cold_after, log_tick, sig_cap);
                     else
-                        nx = run_quiet<H, true, ALIGNED, W, LOG>(T, co, cRf, ncL, spoolf, lf, ctx, n, P.critical_temperature_f32,
+                        nx = run_quiet<H, true, ALIGNED, W, LOG>(diff_form, T, co, cRf, cLf, spoolf, lf, ctx, n, P.critical_temperature_f32,
                                                                  P.breaking_temperature_f32, crit_count, broke, cold_after, log_tick, sig_cap);
                 }
                 s.crit_count = crit_count;
@@ -909,18 +985,8 @@ __device__ __forceinline__ void step_env(const SparcParams &P, const SparcStateP
                         }
                     }
                 }
-                const float2 ncL2 = make_float2(ncL, ncL), cR2 = make_float2(cRf, cRf);
-                const float d_mid = yv - xl;
-                float2 dprev = make_float2(T[0].x - left, d_mid);
-                const float2 dlast = make_float2(d_mid, right - T[H - 1].y);
-#pragma unroll
-                for (int j = 0; j < H; j++) {
-                    const float2 dnext = (j + 1 < H) ? sub2(T[j + 1], T[j]) : dlast;
-                    float2 q = __ffma2_rn(cR2, dnext, acc[j]);
-                    q = __ffma2_rn(ncL2, dprev, q);
-                    dprev = dnext;
-                    T[j] = __fadd2_rn(T[j], q);
-                }
+                if (diff_form) stencil_apply<H, true>(T, acc, make_float2(cRf, cRf), make_float2(cLf, cLf), left, right, xl, yv);
+                else stencil_apply<H, false>(T, acc, make_float2(cRf, cRf), make_float2(cLf, cLf), left, right, xl, yv);
             }
             if (LOG && logging) log_tick();
             // ---- _check_wire_breaking (wire.py:376-388) ---------------------------------------
