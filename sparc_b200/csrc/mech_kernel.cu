@@ -45,7 +45,10 @@ __device__ __forceinline__ bool mech_block_fast(const SparcParams &P, const EnvP
     return !bad;
 }
 
-__global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ SparcParams P,
+#ifndef SPARC_MECH_MAX_THREADS
+#define SPARC_MECH_MAX_THREADS 256     /* largest pre-pass block (envs per block), see mech_launch */
+#endif
+__global__ void __launch_bounds__(SPARC_MECH_MAX_THREADS) mech_kernel(const __grid_constant__ SparcParams P,
                                                    const __grid_constant__ SparcStatePtrs S,
                                                    const __grid_constant__ StepArgs a)
 {
@@ -99,9 +102,27 @@ __global__ void __launch_bounds__(128) mech_kernel(const __grid_constant__ Sparc
     }
 }
 
+// Envs (threads) per pre-pass block.  The threads are independent and latency-bound (~110 cycles per simulated µs),
+// so the block shape only decides HOW MANY SMs host pre-pass warps next to the step kernel's.  Measured (same box,
+// profiles/r02b_exp_prepass2.txt): 32 blocks of 128 at 4096 envs -4.3 % per control step against 128 blocks of 32,
+// 64 blocks of 256 at 16384 envs -2.6 %; 8 blocks of 512 +25 % (sixteen fp64 chains per scheduler).  A 120-register
+// step kernel, which leaves room for the pre-pass blocks beside eight resident step blocks, changes nothing: it is
+// not the register footprint.  Rule: about 32 blocks, at least one warp, at most SPARC_MECH_MAX_THREADS per block.
+static int mech_block_threads(const int n_envs)
+{
+#ifdef SPARC_MECH_THREADS   /* experiments: fixed block size */
+    return SPARC_MECH_THREADS;
+#else
+    int t = 32;
+    while (t < SPARC_MECH_MAX_THREADS && n_envs > 32 * t) t *= 2;
+    return t;
+#endif
+}
+
 void mech_launch(const SparcParams &P, const SparcStatePtrs &S, const StepArgs &a, cudaStream_t stream)
 {
-    mech_kernel<<<(a.n_envs + 31) / 32, 32, 0, stream>>>(P, S, a);   // latency-bound: one warp per SM
+    const int T = mech_block_threads(a.n_envs);
+    mech_kernel<<<(a.n_envs + T - 1) / T, T, 0, stream>>>(P, S, a);
 }
 
 }  // namespace sparc

@@ -205,6 +205,9 @@ __device__ __forceinline__ void stencil_quiet_us(float2 (&T)[H], const Coefs<H, 
     stencil_apply<H, DIFF>(T, acc, cR2, cL2, left, right, xl, yv);
 }
 
+#ifndef SPARC_COLD_UNROLL
+#define SPARC_COLD_UNROLL 2     /* µs per trip of the cold quiet loop (4: 2.2 kB loop body, measured -3 ... -4 %: no_instruction 0.34 -> 0.62 per issue) */
+#endif
 // n quiet µs.  HOT additionally runs _check_wire_breaking (wire.py:376-388) every µs and returns the
 // number of µs executed (n, or k+1 when the wire broke on µs k; `broke` says which).
 template <int H, bool HOT, bool ALIGNED, int W, bool LOG, bool DIFF, class LogTick, class SigCap>
@@ -219,14 +222,15 @@ __device__ __forceinline__ int run_quiet_t(float2 (&T)[H], const Coefs<H, ALIGNE
 #ifdef SPARC_ABL_NOSTENCIL
     if (!HOT) { crit_count = 0; return n; }
 #endif
-    if constexpr (!HOT && !LOG && W == 1) {     // the common case: two µs per trip (halves the loop overhead)
+    if constexpr (!HOT && !LOG && W == 1) {     // the common case: SPARC_COLD_UNROLL µs per trip (halves the loop overhead)
         int k = 0;
 #pragma unroll 1
-        for (; k + 2 <= n; k += 2) {
-            stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
-            stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
+        for (; k + SPARC_COLD_UNROLL <= n; k += SPARC_COLD_UNROLL) {
+#pragma unroll
+            for (int u = 0; u < SPARC_COLD_UNROLL; u++) stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
         }
-        if (k < n) stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
+#pragma unroll 1
+        for (; k < n; k++) stencil_quiet_us<H, ALIGNED, W, DIFF>(T, co, cR2, cL2, spoolf, f, ctx);
         crit_count = 0;
         return n;
     }
@@ -1179,8 +1183,12 @@ template <int K, bool INJECT, int W, bool LOG, bool ALIGNED>
 #ifndef SPARC_WARPS_MULTI
 #define SPARC_WARPS_MULTI 16    /* resident warps per SM the block-per-env variants (W > 1) are sized for */
 #endif
+#ifdef SPARC_MAXNREG            /* experiments: an explicit register cap instead of a residency target */
+__global__ void __maxnreg__(SPARC_MAXNREG)
+#else
 __global__ void __launch_bounds__(W == 1 ? SPARC_BLOCK_THREADS : 32 * W,
                                   W == 1 ? min_blocks_for(K, ALIGNED) : (SPARC_WARPS_MULTI / W > 0 ? SPARC_WARPS_MULTI / W : 1))
+#endif
 step_kernel(const __grid_constant__ SparcParams P, const __grid_constant__ SparcStatePtrs S,
             const __grid_constant__ StepArgs a)
 {
