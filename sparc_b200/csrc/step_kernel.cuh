@@ -12,7 +12,7 @@
 //     the round-1 kernel held 36 coefficient registers and ~40 scalars and carried 168 bytes of spills at 128
 //     registers.  The kernel also compiles to 72 registers (28 warps/SM); measured, more resident warps do not
 //     help (the kernel is bound by instruction dispatch, profiles/r02_experiments.txt), so it ships at 128
-//     registers / 16 warps per SM with 16 bytes of spills.
+//     registers / 16 warps per SM with 8 bytes of spills.
 //   * REGION LAYOUT (SparcLayout, step_common.cuh).  Zone boundaries, the zero-flux end and the pad
 //     slots used to be per-cell coefficient registers (cE, c0, cR per cell).  Now the cells are laid out
 //     so that every such boundary falls between two HALVES of a lane: the conduction coefficient is one
@@ -206,7 +206,7 @@ __device__ __forceinline__ void stencil_quiet_us(float2 (&T)[H], const Coefs<H, 
 }
 
 #ifndef SPARC_COLD_UNROLL
-#define SPARC_COLD_UNROLL 2     /* µs per trip of the cold quiet loop (4: 2.2 kB loop body, measured -3 ... -4 %: no_instruction 0.34 -> 0.62 per issue) */
+#define SPARC_COLD_UNROLL 2     /* µs per trip of the cold quiet loop (4: one instruction per µs fewer, but the 2.2 kB loop body measured +3 ... +4 % time: no_instruction 0.34 -> 0.62 per issue) */
 #endif
 // n quiet µs.  HOT additionally runs _check_wire_breaking (wire.py:376-388) every µs and returns the
 // number of µs executed (n, or k+1 when the wire broke on µs k; `broke` says which).
